@@ -1,0 +1,50 @@
+"""Field order of the p3_main argument structs as flattened by the C ABI (include/p3_b200.h).
+
+Mirrors P3PrognosticState / P3DiagnosticInputs / P3DiagnosticOutputs / P3HistoryOnly
+(reference: components/eamxx/src/physics/p3/p3_functions.hpp:161-276).
+"""
+
+PROGNOSTIC = ["qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm", "qv", "th"]
+DIAG_INPUTS = ["nc_nuceat_tend", "nccn", "ni_activated", "inv_qc_relvar", "cld_frac_i", "cld_frac_l",
+               "cld_frac_r", "pres", "dz", "dpres", "inv_exner", "qv_prev", "t_prev"]
+DIAG_OUTPUTS_2D = ["qv2qi_depos_tend", "diag_eff_radius_qc", "diag_eff_radius_qi", "diag_eff_radius_qr",
+                   "rho_qi", "precip_liq_flux", "precip_ice_flux", "precip_total_tend", "nevapr"]
+HISTORY = ["liq_ice_exchange", "vap_liq_exchange", "vap_ice_exchange"]
+SURFACE_1D = ["precip_liq_surf", "precip_ice_surf"]
+
+FIELDS = PROGNOSTIC + DIAG_INPUTS + DIAG_OUTPUTS_2D + HISTORY + SURFACE_1D
+NUM_FIELDS = len(FIELDS)            # 37
+INDEX = {n: i for i, n in enumerate(FIELDS)}
+
+# fields with nlev+1 levels (p3_functions.hpp:232-235, "pverp")
+INTERFACE_FIELDS = ("precip_liq_flux", "precip_ice_flux")
+OUTPUTS = PROGNOSTIC + DIAG_OUTPUTS_2D + HISTORY + SURFACE_1D
+
+# integer diagnostics exported per column (bit-exact parity targets)
+DIAG_NAMES = ["nucleationPossible", "hydrometeorsPresent_part1", "hydrometeorsPresent_part2",
+              "qc_ktop", "qc_kbot", "qc_nsub", "qr_ktop", "qr_kbot", "qr_nsub",
+              "qi_ktop", "qi_kbot", "qi_nsub", "error", "pad13", "pad14", "pad15"]
+NUM_DIAG = 16
+
+# P3Runtime (p3_functions.hpp:112-133): order of the 20 values passed through the C ABI
+RUNTIME_DEFAULTS = [
+    ("max_total_ni", 740.0e3), ("autoconversion_prefactor", 1350.0), ("autoconversion_qc_exponent", 2.47),
+    ("autoconversion_nc_exponent", 1.79), ("autoconversion_radius", 25.0e-6), ("accretion_prefactor", 67.0),
+    ("accretion_qc_exponent", 1.15), ("accretion_qr_exponent", 1.15), ("rain_selfcollection_prefactor", 5.78),
+    ("rain_selfcollection_breakup_diameter", 0.00028), ("constant_mu_rain", 1.0), ("spa_ccn_to_nc_factor", 1.0),
+    ("cldliq_to_ice_collection_factor", 0.5), ("rain_to_ice_collection_factor", 1.0), ("min_rime_rho", 50.0),
+    ("max_rime_rho", 900.0), ("immersion_freezing_exponent", 0.65), ("deposition_nucleation_exponent", 0.304),
+    ("ice_sedimentation_factor", 1.0), ("do_ice_production", 1.0),
+]
+
+
+def levels_of(name, nlev):
+    if name in SURFACE_1D:
+        return 1
+    return nlev + 1 if name in INTERFACE_FIELDS else nlev
+
+
+def algorithmic_bytes_per_col_level(real_bytes, predict_nc=True, prescribed_ccn=True):
+    """SURVEY.md §8(d) / BASELINE.md §3: every live interface array touched once."""
+    reads = 19 + (1 if prescribed_ccn else 0) + (2 if (predict_nc and not prescribed_ccn) else 0)
+    return (reads + 22) * real_bytes
