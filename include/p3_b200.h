@@ -1,0 +1,206 @@
+/*
+ * p3_b200.h — C ABI of the B200-native P3 microphysics column driver (libp3b200.so).
+ *
+ * This is the drop-in boundary for ONE hot path of EAMxx/SCREAM: p3::Functions<S,D>::p3_main
+ * (reference: components/eamxx/src/physics/p3/p3_functions.hpp:1356-1369, implementation
+ * p3/impl/p3_main_impl.hpp:76-372) and its callers P3Microphysics::run_impl
+ * (p3/eamxx_p3_run.cpp:5-46) and the test bridge p3_main_f (p3/p3_functions_f90.cpp:1888-2103).
+ *
+ * Rules of the boundary
+ *   - plain C: pointers, sizes, PODs; no C++/torch/Kokkos types; no exceptions cross it;
+ *   - every entry point returns 0 on success or a negative P3B200_E* code; p3b200_strerror() names it;
+ *   - p3b200_main takes DEVICE pointers only.  There is no CPU fallback: without a CUDA device
+ *     p3b200_create fails with P3B200_ECUDA;
+ *   - the caller owns all field memory; the handle owns the lookup tables, the per-column integer
+ *     diagnostics and the work-queue counter;
+ *   - field arrays are (ncol, nlev) with the LEVEL index contiguous (Kokkos LayoutRight views of the
+ *     reference, p3_functions.hpp:161-276) and a per-field column stride in ELEMENTS (tracer
+ *     sub-views of a bundled array have stride > nlev, share/field/field_impl.hpp:880-909);
+ *     level 0 is the model top (p3_main_impl.hpp:97-99: kdir=-1, ktop=0, kbot=nk-1).
+ */
+#ifndef P3_B200_H
+#define P3_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define P3B200_ABI_VERSION 1
+
+/* error codes */
+#define P3B200_OK        0
+#define P3B200_EINVAL   -1   /* bad argument (null pointer, nlev out of range, real_bytes not 4/8 ...) */
+#define P3B200_ECUDA    -2   /* CUDA runtime error (no device, launch failure ...); see p3b200_last_cuda_error */
+#define P3B200_ENOMEM   -3   /* host or device allocation failed */
+#define P3B200_ETABLE   -4   /* lookup-table blob/text malformed or wrong version (p3_table_ice_impl.hpp:40-41) */
+#define P3B200_ECOLUMN  -5   /* a column raised a physics error flag (T<=0 / NaN / Co_max<0), see diag[P3B200_D_ERROR] */
+
+#define P3B200_MAX_NLEV 256  /* levels per column supported by the warp-per-column layout (8 per lane) */
+
+/* Table extents: P3C, p3_functions.hpp:30-52 */
+#define P3B200_DENSIZE 5
+#define P3B200_RIMSIZE 4
+#define P3B200_ISIZE 50
+#define P3B200_ICE_TABLE_SIZE 12
+#define P3B200_RCOLLSIZE 30
+#define P3B200_COLLECT_TABLE_SIZE 2
+#define P3B200_VTABLE_DIM0 300
+#define P3B200_VTABLE_DIM1 10
+#define P3B200_MU_R_TABLE_DIM 150
+#define P3B200_DNUSIZE 16
+
+/* P3LookupTables (p3_functions.hpp:279-290), host side, always double; converted to the run
+ * precision on upload.  collect_table_vals holds log10 of the file values exactly as
+ * init_kokkos_ice_lookup_tables stores them (p3_table_ice_impl.hpp:63). */
+typedef struct P3B200Tables {
+  double mu_r_table_vals[P3B200_MU_R_TABLE_DIM];
+  double vn_table_vals[P3B200_VTABLE_DIM0][P3B200_VTABLE_DIM1];
+  double vm_table_vals[P3B200_VTABLE_DIM0][P3B200_VTABLE_DIM1];
+  double revap_table_vals[P3B200_VTABLE_DIM0][P3B200_VTABLE_DIM1];
+  double ice_table_vals[P3B200_DENSIZE][P3B200_RIMSIZE][P3B200_ISIZE][P3B200_ICE_TABLE_SIZE];
+  double collect_table_vals[P3B200_DENSIZE][P3B200_RIMSIZE][P3B200_ISIZE][P3B200_RCOLLSIZE][P3B200_COLLECT_TABLE_SIZE];
+  double dnu_table_vals[P3B200_DNUSIZE];
+} P3B200Tables;
+
+/* P3Runtime (p3_functions.hpp:112-158): the 19 scalar knobs + do_ice_production, same names,
+ * same defaults (p3b200_runtime_defaults). */
+typedef struct P3B200Runtime {
+  double max_total_ni;
+  double autoconversion_prefactor;
+  double autoconversion_qc_exponent;
+  double autoconversion_nc_exponent;
+  double autoconversion_radius;
+  double accretion_prefactor;
+  double accretion_qc_exponent;
+  double accretion_qr_exponent;
+  double rain_selfcollection_prefactor;
+  double rain_selfcollection_breakup_diameter;
+  double constant_mu_rain;
+  double spa_ccn_to_nc_factor;
+  double cldliq_to_ice_collection_factor;
+  double rain_to_ice_collection_factor;
+  double min_rime_rho;
+  double max_rime_rho;
+  double immersion_freezing_exponent;
+  double deposition_nucleation_exponent;
+  double ice_sedimentation_factor;
+  int32_t do_ice_production;
+  int32_t pad_;
+} P3B200Runtime;
+
+/* Flattened field order of P3PrognosticState (:161-183), P3DiagnosticInputs (:186-214),
+ * P3DiagnosticOutputs (:217-241), P3HistoryOnly (:268-276). */
+enum P3B200Field {
+  P3B200_F_QC = 0, P3B200_F_NC, P3B200_F_QR, P3B200_F_NR, P3B200_F_QI, P3B200_F_QM, P3B200_F_NI,
+  P3B200_F_BM, P3B200_F_QV, P3B200_F_TH,                                   /* prognostic, in/out */
+  P3B200_F_NC_NUCEAT_TEND, P3B200_F_NCCN, P3B200_F_NI_ACTIVATED, P3B200_F_INV_QC_RELVAR,
+  P3B200_F_CLD_FRAC_I, P3B200_F_CLD_FRAC_L, P3B200_F_CLD_FRAC_R, P3B200_F_PRES, P3B200_F_DZ,
+  P3B200_F_DPRES, P3B200_F_INV_EXNER, P3B200_F_QV_PREV, P3B200_F_T_PREV,   /* diagnostic inputs */
+  P3B200_F_QV2QI_DEPOS_TEND, P3B200_F_DIAG_EFF_RADIUS_QC, P3B200_F_DIAG_EFF_RADIUS_QI,
+  P3B200_F_DIAG_EFF_RADIUS_QR, P3B200_F_RHO_QI, P3B200_F_PRECIP_LIQ_FLUX /* nlev+1 */,
+  P3B200_F_PRECIP_ICE_FLUX /* nlev+1 */, P3B200_F_PRECIP_TOTAL_TEND, P3B200_F_NEVAPR, /* diag outputs */
+  P3B200_F_LIQ_ICE_EXCHANGE, P3B200_F_VAP_LIQ_EXCHANGE, P3B200_F_VAP_ICE_EXCHANGE,    /* history */
+  P3B200_F_PRECIP_LIQ_SURF /* [ncol] */, P3B200_F_PRECIP_ICE_SURF /* [ncol] */,
+  P3B200_F_NUM
+};
+
+/* One array per field: device pointer + column stride in elements (ignored for the two [ncol] arrays).
+ * P3B200_F_INV_QC_RELVAR, and the flag-dependent inputs that are dead for the chosen flags, may be NULL. */
+typedef struct P3B200Fields {
+  void*   ptr[P3B200_F_NUM];
+  int64_t col_stride[P3B200_F_NUM];
+} P3B200Fields;
+
+/* P3Infrastructure (p3_functions.hpp:244-264).  its/ite/kts/kte are implied by ncol/nlev
+ * (p3_main is always called with the whole local range, eamxx_p3_process_interface.cpp:329-334). */
+typedef struct P3B200Infra {
+  double  dt;
+  int32_t it;
+  int32_t ncol;            /* nj */
+  int32_t nlev;            /* nk, 1..P3B200_MAX_NLEV */
+  int32_t predictNc;
+  int32_t prescribedCCN;
+  int32_t zero_flux_top;   /* 1: also zero precip_*_flux[nlev] (what p3_main_f's pre-zeroing achieves,
+                              p3_functions_f90.cpp:1941-1945); 0: reference p3_main pack-size-1 behaviour */
+} P3B200Infra;
+
+/* Per-column integer diagnostics (bit-exact parity targets), P3B200_D_NUM int32 per column. */
+enum P3B200Diag {
+  P3B200_D_NUC_POSSIBLE = 0, P3B200_D_HYDRO_PART1, P3B200_D_HYDRO_PART2,
+  P3B200_D_QC_KTOP, P3B200_D_QC_KBOT, P3B200_D_QC_NSUB,
+  P3B200_D_QR_KTOP, P3B200_D_QR_KBOT, P3B200_D_QR_NSUB,
+  P3B200_D_QI_KTOP, P3B200_D_QI_KBOT, P3B200_D_QI_NSUB,
+  P3B200_D_ERROR,          /* bit0 T<=0, bit1 T NaN (physics_saturation_impl.hpp:29,33), bit2 Co_max<0 (p3_upwind_impl.hpp:108) */
+  P3B200_D_NUM = 16
+};
+
+typedef struct p3b200_ctx* p3b200_handle;
+
+/* ---- library ---------------------------------------------------------------------------------- */
+int         p3b200_abi_version(void);
+const char* p3b200_strerror(int code);
+const char* p3b200_last_cuda_error(void);
+int         p3b200_device_count(void);                 /* >=0, or P3B200_ECUDA */
+
+/* ---- tables: replaces init_kokkos_ice_lookup_tables (p3_table_ice_impl.hpp:18-78), init_kokkos_tables
+ *      (p3_table3_impl.hpp:87-148) and the Fortran generator p3_init_b (micro_p3.F90:218-341). ------- */
+void p3b200_runtime_defaults(P3B200Runtime* out);       /* P3Runtime defaults, p3_functions.hpp:114-133 */
+/* Parse the reference's text table "p3_lookup_table_1.dat-v<version>" into ice/collect (log10 applied). */
+int  p3b200_tables_read_text(const char* path, const char* expect_version, P3B200Tables* out);
+/* Load the binary blob written by tools/make_table_blob.py (raw doubles; log10 applied on load). */
+int  p3b200_tables_read_blob(const char* path, const char* expect_version, P3B200Tables* out);
+/* Generate mu_r/vn/vm/revap by the p3_init_b quadrature and fill dnu (p3_table3_impl.hpp:120-135). */
+int  p3b200_tables_generate_rain(P3B200Tables* out);
+
+/* ---- handle ------------------------------------------------------------------------------------ */
+/* real_bytes: 8 (SCREAM_DOUBLE_PRECISION) or 4.  device: CUDA ordinal.  Tables are copied to the device. */
+int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p3b200_handle* out);
+int p3b200_destroy(p3b200_handle h);
+
+/* p3_main on DEVICE arrays.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = default stream)
+ * unless elapsed_us != NULL, in which case it synchronises and returns the device time of the
+ * launch in microseconds like p3_main does (p3_main_impl.hpp:105,326-330).
+ * diag_dev: optional device int32[ncol*P3B200_D_NUM]; NULL = keep them in the handle
+ * (p3b200_get_diag). */
+int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev);
+
+/* Copy the integer diagnostics of the last p3b200_main (diag_dev == NULL) to the host. */
+int p3b200_get_diag(p3b200_handle h, int32_t* host_out, int32_t ncol);
+/* OR of diag[P3B200_D_ERROR] over the columns of the last call (synchronises). 0 = clean. */
+int p3b200_error_summary(p3b200_handle h, int32_t* or_of_error_bits);
+
+/* Same as p3b200_main with HOST arrays (same layout): pinned staging, column-chunked H2D -> kernel ->
+ * D2H pipeline on internal streams.  This is the shape of P3Microphysics::run_impl for a host-resident
+ * field manager and the e2e leg of bench.py.  Returns wall microseconds in elapsed_us. */
+int p3b200_main_host(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* host_fields,
+                     const P3B200Infra* infra, int64_t* elapsed_us, int32_t* diag_host);
+
+/* Device kernel time (ms) of the last p3b200_main/p3b200_main_host measured with CUDA events on the
+ * launching stream(s) (sum over chunks); synchronises. */
+int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches);
+
+/* ---- the reference's own C bridge, re-implemented on the GPU ---------------------------------------
+ * Drop-in for p3_main_f (p3_functions_f90.hpp:945-952; p3_functions_f90.cpp:1888-2103): HOST pointers,
+ * Fortran (column-major) layout arr[i + ncol*k], 1-based its/kts (must be 1), outputs zeroed on entry.
+ * Real is double (p3_main_f) or float (p3_main_f_sp).  Uses a process-wide default handle created on
+ * first use from p3b200_set_default_tables().  Returns elapsed microseconds (>=0) or a negative error. */
+int p3b200_set_default_tables(const P3B200Tables* host_tables, int device);
+int p3b200_p3_main_f(
+  double* qc, double* nc, double* qr, double* nr, double* th_atm, double* qv, double dt,
+  double* qi, double* qm, double* ni, double* bm, double* pres, double* dz,
+  double* nc_nuceat_tend, double* nccn_prescribed, double* ni_activated, double* inv_qc_relvar, int it,
+  double* precip_liq_surf, double* precip_ice_surf, int its, int ite, int kts, int kte,
+  double* diag_eff_radius_qc, double* diag_eff_radius_qi, double* diag_eff_radius_qr, double* rho_qi,
+  int do_predict_nc, int do_prescribed_CCN, double* dpres, double* inv_exner,
+  double* qv2qi_depos_tend, double* precip_liq_flux, double* precip_ice_flux,
+  double* cld_frac_r, double* cld_frac_l, double* cld_frac_i,
+  double* liq_ice_exchange, double* vap_liq_exchange, double* vap_ice_exchange,
+  double* qv_prev, double* t_prev);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* P3_B200_H */

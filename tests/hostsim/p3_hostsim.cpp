@@ -1,0 +1,62 @@
+// tests/hostsim — DEBUG/TEST BUILD ONLY.  Compiles the product's column driver
+// (scream_b200/csrc/p3_column.cuh, the exact source the CUDA kernel instantiates) for the host with a
+// 1-lane "warp" so that control flow, indexing and shared-row reuse can be checked against the oracle
+// in a container that has no GPU.  It is never loaded by the product package, bench.py's GPU arm or
+// the C ABI: libp3b200.so has no CPU path.
+#include "../../scream_b200/csrc/p3_column.cuh"
+#include "../../scream_b200/csrc/p3_host.hpp"
+
+#include <vector>
+
+namespace {
+struct WarpSim {
+  static constexpr int size = 1;
+  int lane() const { return 0; }
+  bool any(bool b) const { return b; }
+  template <class R> R max_real(R v) const { return v; }
+  int min_int(int v) const { return v; }
+  int max_int(int v) const { return v; }
+  int or_int(int v) const { return v; }
+  void sync() const {}
+};
+
+template <typename Real>
+int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int ncol, int nlev, double dt,
+        int predictNc, int prescribedCCN, int zero_flux_top, const P3B200Runtime* rt, int* diag) {
+  using namespace p3b200;
+  std::vector<Real> ice(12000), coll(60000), vn(3000), vm(3000), revap(3000);
+  for (int i = 0; i < 12000; ++i) ice[i] = Real((&t->ice_table_vals[0][0][0][0])[i]);
+  for (int i = 0; i < 60000; ++i) coll[i] = Real((&t->collect_table_vals[0][0][0][0][0])[i]);
+  for (int i = 0; i < 3000; ++i) {
+    vn[i] = Real((&t->vn_table_vals[0][0])[i]); vm[i] = Real((&t->vm_table_vals[0][0])[i]);
+    revap[i] = Real((&t->revap_table_vals[0][0])[i]);
+  }
+  MainArgs<Real> a;
+  for (int f = 0; f < F_NUM; ++f) { a.f[f] = static_cast<Real*>(fields[f]); a.stride[f] = strides[f]; }
+  a.ncol = ncol; a.nk = nlev; a.dt = Real(dt); a.predictNc = predictNc; a.prescribedCCN = prescribedCCN;
+  a.zero_flux_top = zero_flux_top;
+  a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data()};
+  P3B200Runtime r;
+  if (rt) r = *rt; else runtime_defaults(r);
+  a.ro = make_runtime<Real>(r);
+  a.diag = diag; a.queue = nullptr;
+  std::vector<Real> smem(size_t(NUM_SMEM_ROWS) * nlev);
+  WarpSim w;
+  for (int i = 0; i < ncol; ++i) Column<Real, WarpSim>::run(w, a, i, smem.data());
+  return 0;
+}
+}  // namespace
+
+extern "C" int p3sim_main(const P3B200Tables* t, int real_bytes, void* const* fields, const int64_t* strides,
+                          int ncol, int nlev, double dt, int predictNc, int prescribedCCN, int zero_flux_top,
+                          const P3B200Runtime* rt, int* diag) {
+  if (real_bytes == 8) return run<double>(t, fields, strides, ncol, nlev, dt, predictNc, prescribedCCN, zero_flux_top, rt, diag);
+  if (real_bytes == 4) return run<float>(t, fields, strides, ncol, nlev, dt, predictNc, prescribedCCN, zero_flux_top, rt, diag);
+  return -1;
+}
+extern "C" int p3sim_tables(const char* blob, P3B200Tables* out) {
+  int rc = p3b200::tables_read_blob(blob, "4.1.1", *out);
+  if (rc) return rc;
+  p3b200::tables_generate_rain(*out);
+  return 0;
+}
