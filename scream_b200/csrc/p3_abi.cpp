@@ -1,0 +1,313 @@
+// p3_abi.cpp — the extern "C" surface of libp3b200.so declared in include/p3_b200.h.
+//
+// Host-only C++ (CUDA runtime API, no device code): owns the handle (device tables, integer
+// diagnostics, work-queue counters, events, the host<->device staging pipeline) and forwards to
+// the kernel TU (p3_kernel.cu).  There is no CPU implementation of p3_main behind this file:
+// every compute entry point fails with P3B200_ECUDA when no CUDA device is usable.
+#include "p3_host.hpp"
+#include "p3_kernel.cuh"
+
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace p3b200;
+
+namespace {
+
+thread_local std::string g_last_cuda_error;
+
+int cuda_fail(cudaError_t e, const char* what) {
+  g_last_cuda_error = std::string(what) + ": " + cudaGetErrorString(e);
+  return P3B200_ECUDA;
+}
+#define CU(call)                                            \
+  do {                                                      \
+    cudaError_t e__ = (call);                               \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call);   \
+  } while (0)
+
+constexpr int NQUEUE = 64;        // ring of work-queue counters so launches on different streams never share one
+constexpr int NSLOT = 3;          // host pipeline depth (H2D / kernel / D2H in flight)
+
+struct EventPair { cudaEvent_t a = nullptr, b = nullptr; };
+
+struct Slot {                     // one in-flight column chunk of p3b200_main_host
+  cudaStream_t stream = nullptr;
+  void* dev = nullptr;            // chunk arrays, all 2-D fields padded to nlev+1
+  size_t dev_bytes = 0;
+  int* diag = nullptr;
+  size_t diag_cols = 0;
+};
+
+}  // namespace
+
+struct p3b200_ctx {
+  int device = 0;
+  int real_bytes = 8;
+  void* d_tables = nullptr;       // ice | coll | vn | vm | revap in run precision
+  Tables<double> tbd{};
+  Tables<float> tbf{};
+  int* d_diag = nullptr;
+  size_t diag_cols = 0;
+  unsigned int* d_queue = nullptr;
+  int next_queue = 0;
+  std::vector<EventPair> events;  // one pair per kernel launch of the last call
+  size_t events_used = 0;
+  int last_ncol = 0;
+  bool last_diag_in_handle = false;
+  Slot slots[NSLOT];
+  LaunchConfig cfg{};
+  int cfg_nk = -1, cfg_ncol = -1;
+};
+
+namespace {
+
+template <typename Real>
+int upload_tables(p3b200_ctx* h, const P3B200Tables& t) {
+  const size_t n_ice = 12000, n_coll = 60000, n_v = 3000;
+  const size_t total = n_ice + n_coll + 3 * n_v;
+  std::vector<Real> host(total);
+  size_t o = 0;
+  const double* src = &t.ice_table_vals[0][0][0][0];
+  for (size_t i = 0; i < n_ice; ++i) host[o + i] = Real(src[i]);
+  o += n_ice;
+  src = &t.collect_table_vals[0][0][0][0][0];
+  for (size_t i = 0; i < n_coll; ++i) host[o + i] = Real(src[i]);
+  o += n_coll;
+  const double* vs[3] = {&t.vn_table_vals[0][0], &t.vm_table_vals[0][0], &t.revap_table_vals[0][0]};
+  for (int v = 0; v < 3; ++v) {
+    for (size_t i = 0; i < n_v; ++i) host[o + i] = Real(vs[v][i]);
+    o += n_v;
+  }
+  CU(cudaMalloc(&h->d_tables, total * sizeof(Real)));
+  CU(cudaMemcpy(h->d_tables, host.data(), total * sizeof(Real), cudaMemcpyHostToDevice));
+  const Real* base = static_cast<const Real*>(h->d_tables);
+  Tables<Real> tb{base, base + n_ice, base + n_ice + n_coll, base + n_ice + n_coll + n_v, base + n_ice + n_coll + 2 * n_v};
+  if constexpr (sizeof(Real) == 8) h->tbd = tb; else h->tbf = tb;
+  return P3B200_OK;
+}
+
+int ensure_events(p3b200_ctx* h, size_t n) {
+  while (h->events.size() < n) {
+    EventPair p;
+    CU(cudaEventCreate(&p.a));
+    CU(cudaEventCreate(&p.b));
+    h->events.push_back(p);
+  }
+  return P3B200_OK;
+}
+
+int validate(const P3B200Fields* f, const P3B200Infra* in) {
+  if (!f || !in) return P3B200_EINVAL;
+  if (in->ncol < 0 || in->nlev < 1 || in->nlev > P3B200_MAX_NLEV || !(in->dt > 0)) return P3B200_EINVAL;
+  for (int i = 0; i < P3B200_F_NUM; ++i) {
+    const bool optional = (i == P3B200_F_INV_QC_RELVAR) ||
+                          (i == P3B200_F_NCCN && !in->prescribedCCN) ||
+                          ((i == P3B200_F_NC_NUCEAT_TEND || i == P3B200_F_NI_ACTIVATED) &&
+                           (in->prescribedCCN || !in->predictNc));
+    if (!f->ptr[i] && !optional) return P3B200_EINVAL;
+    if (f->ptr[i] && i < P3B200_F_PRECIP_LIQ_SURF) {
+      const int lev = (i == P3B200_F_PRECIP_LIQ_FLUX || i == P3B200_F_PRECIP_ICE_FLUX) ? in->nlev + 1 : in->nlev;
+      if (f->col_stride[i] < lev) return P3B200_EINVAL;
+    }
+  }
+  return P3B200_OK;
+}
+
+// Enqueue one kernel launch over `ncol` columns of device arrays.  ev (optional) brackets it.
+template <typename Real>
+int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
+            int ncol, cudaStream_t stream, int* diag, const EventPair* ev) {
+  MainArgs<Real> a;
+  for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<Real*>(f->ptr[i]); a.stride[i] = f->col_stride[i]; }
+  a.ncol = ncol; a.nk = in->nlev; a.dt = Real(in->dt);
+  a.predictNc = in->predictNc; a.prescribedCCN = in->prescribedCCN; a.zero_flux_top = in->zero_flux_top;
+  if constexpr (sizeof(Real) == 8) a.tb = h->tbd; else a.tb = h->tbf;
+  P3B200Runtime r;
+  if (runtime) r = *runtime; else runtime_defaults(r);
+  a.ro = make_runtime<Real>(r);
+  a.diag = diag;
+  a.queue = h->d_queue + h->next_queue;
+  h->next_queue = (h->next_queue + 1) % NQUEUE;
+  if (h->cfg_nk != in->nlev || h->cfg_ncol != ncol) {
+    const int rc = plan_launch<Real>(in->nlev, ncol, &h->cfg);
+    if (rc) return cuda_fail((cudaError_t)rc, "plan_launch");
+    h->cfg_nk = in->nlev; h->cfg_ncol = ncol;
+  }
+  CU(cudaMemsetAsync(a.queue, 0, sizeof(unsigned int), stream));
+  if (ev) CU(cudaEventRecord(ev->a, stream));
+  const int rc = launch_main<Real>(a, h->cfg, stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_main_kernel launch");
+  if (ev) CU(cudaEventRecord(ev->b, stream));
+  return P3B200_OK;
+}
+
+int enqueue_any(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
+                int ncol, cudaStream_t stream, int* diag, const EventPair* ev) {
+  return h->real_bytes == 8 ? enqueue<double>(h, runtime, f, in, ncol, stream, diag, ev)
+                            : enqueue<float>(h, runtime, f, in, ncol, stream, diag, ev);
+}
+
+}  // namespace
+
+extern "C" {
+
+int p3b200_abi_version(void) { return P3B200_ABI_VERSION; }
+
+const char* p3b200_strerror(int code) {
+  switch (code) {
+    case P3B200_OK: return "ok";
+    case P3B200_EINVAL: return "invalid argument";
+    case P3B200_ECUDA: return "CUDA runtime error (see p3b200_last_cuda_error)";
+    case P3B200_ENOMEM: return "out of memory";
+    case P3B200_ETABLE: return "lookup table malformed or wrong version";
+    case P3B200_ECOLUMN: return "a column raised a physics error flag";
+    default: return "unknown error";
+  }
+}
+
+const char* p3b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
+
+int p3b200_device_count(void) {
+  int n = 0;
+  const cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { cuda_fail(e, "cudaGetDeviceCount"); return P3B200_ECUDA; }
+  return n;
+}
+
+void p3b200_runtime_defaults(P3B200Runtime* out) { if (out) runtime_defaults(*out); }
+
+int p3b200_tables_read_text(const char* path, const char* expect_version, P3B200Tables* out) {
+  if (!out) return P3B200_EINVAL;
+  return tables_read_text(path, expect_version, *out);
+}
+int p3b200_tables_read_blob(const char* path, const char* expect_version, P3B200Tables* out) {
+  if (!out) return P3B200_EINVAL;
+  return tables_read_blob(path, expect_version, *out);
+}
+int p3b200_tables_generate_rain(P3B200Tables* out) {
+  if (!out) return P3B200_EINVAL;
+  tables_generate_rain(*out);
+  return P3B200_OK;
+}
+
+int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p3b200_handle* out) {
+  if (!host_tables || !out || (real_bytes != 4 && real_bytes != 8)) return P3B200_EINVAL;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+  if (device < 0 || device >= n) { g_last_cuda_error = "no such CUDA device"; return P3B200_ECUDA; }
+  CU(cudaSetDevice(device));
+  p3b200_ctx* h = new (std::nothrow) p3b200_ctx;
+  if (!h) return P3B200_ENOMEM;
+  h->device = device;
+  h->real_bytes = real_bytes;
+  int rc = real_bytes == 8 ? upload_tables<double>(h, *host_tables) : upload_tables<float>(h, *host_tables);
+  if (rc == P3B200_OK) {
+    e = cudaMalloc(&h->d_queue, NQUEUE * sizeof(unsigned int));
+    if (e != cudaSuccess) rc = cuda_fail(e, "cudaMalloc queue");
+  }
+  if (rc != P3B200_OK) { p3b200_destroy(h); return rc; }
+  *out = h;
+  return P3B200_OK;
+}
+
+int p3b200_destroy(p3b200_handle h) {
+  if (!h) return P3B200_EINVAL;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (auto& p : h->events) { if (p.a) cudaEventDestroy(p.a); if (p.b) cudaEventDestroy(p.b); }
+  for (auto& s : h->slots) {
+    if (s.dev) cudaFree(s.dev);
+    if (s.diag) cudaFree(s.diag);
+    if (s.stream) cudaStreamDestroy(s.stream);
+  }
+  if (h->d_tables) cudaFree(h->d_tables);
+  if (h->d_diag) cudaFree(h->d_diag);
+  if (h->d_queue) cudaFree(h->d_queue);
+  delete h;
+  return P3B200_OK;
+}
+
+int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev) {
+  if (!h) return P3B200_EINVAL;
+  int rc = validate(fields, infra);
+  if (rc) return rc;
+  CU(cudaSetDevice(h->device));
+  if (elapsed_us) *elapsed_us = 0;
+  h->events_used = 0;
+  h->last_ncol = infra->ncol;
+  h->last_diag_in_handle = (diag_dev == nullptr);
+  if (infra->ncol == 0) return P3B200_OK;
+  int* diag = diag_dev;
+  if (!diag) {
+    if (h->diag_cols < (size_t)infra->ncol) {
+      if (h->d_diag) { CU(cudaFree(h->d_diag)); h->d_diag = nullptr; h->diag_cols = 0; }
+      CU(cudaMalloc(&h->d_diag, (size_t)infra->ncol * D_NUM * sizeof(int)));
+      h->diag_cols = infra->ncol;
+    }
+    diag = h->d_diag;
+  }
+  rc = ensure_events(h, 1);
+  if (rc) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  rc = enqueue_any(h, runtime, fields, infra, infra->ncol, stream, diag, &h->events[0]);
+  if (rc) return rc;
+  h->events_used = 1;
+  if (elapsed_us) {
+    CU(cudaEventSynchronize(h->events[0].b));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, h->events[0].a, h->events[0].b));
+    *elapsed_us = (int64_t)(ms * 1000.0f + 0.5f);
+  }
+  return P3B200_OK;
+}
+
+int p3b200_get_diag(p3b200_handle h, int32_t* host_out, int32_t ncol) {
+  if (!h || !host_out || ncol < 0) return P3B200_EINVAL;
+  if (!h->last_diag_in_handle || (size_t)ncol > h->diag_cols || ncol > h->last_ncol) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(host_out, h->d_diag, (size_t)ncol * D_NUM * sizeof(int), cudaMemcpyDeviceToHost));
+  return P3B200_OK;
+}
+
+int p3b200_error_summary(p3b200_handle h, int32_t* or_of_error_bits) {
+  if (!h || !or_of_error_bits) return P3B200_EINVAL;
+  *or_of_error_bits = 0;
+  if (!h->last_diag_in_handle || h->last_ncol == 0) return P3B200_OK;
+  std::vector<int32_t> d((size_t)h->last_ncol * D_NUM);
+  const int rc = p3b200_get_diag(h, d.data(), h->last_ncol);
+  if (rc) return rc;
+  int32_t acc = 0;
+  for (int i = 0; i < h->last_ncol; ++i) acc |= d[(size_t)i * D_NUM + D_ERROR];
+  *or_of_error_bits = acc;
+  return P3B200_OK;
+}
+
+int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches) {
+  if (!h || !ms) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  double total = 0;
+  for (size_t i = 0; i < h->events_used; ++i) {
+    CU(cudaEventSynchronize(h->events[i].b));
+    float t = 0;
+    CU(cudaEventElapsedTime(&t, h->events[i].a, h->events[i].b));
+    total += t;
+  }
+  *ms = total;
+  if (launches) *launches = (int64_t)h->events_used;
+  return P3B200_OK;
+}
+
+}  // extern "C"
+
+#include "p3_abi_host.inc"

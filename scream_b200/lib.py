@@ -1,0 +1,248 @@
+"""ctypes binding of the product library libp3b200.so (C ABI: include/p3_b200.h).
+
+This is plumbing only: torch supplies device memory and streams, numpy supplies host arrays; every
+P3 computation happens in the sm_100a kernel behind p3b200_main / p3b200_main_host.  There is no CPU
+fallback: importing works without a GPU (so the ABI can be inspected), creating a handle does not.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+from .fields import FIELDS, INTERFACE_FIELDS, NUM_DIAG, RUNTIME_DEFAULTS, SURFACE_1D
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libp3b200.so")
+TABLE_BLOB = os.path.join(PKG_DIR, "data", "p3_lookup_table_1.v4.1.1.f64")
+NUM_FIELDS = len(FIELDS)
+
+# every symbol include/p3_b200.h declares
+ABI_SYMBOLS = [
+    "p3b200_abi_version", "p3b200_strerror", "p3b200_last_cuda_error", "p3b200_device_count",
+    "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
+    "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
+    "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_set_default_tables",
+    "p3b200_p3_main_f",
+]
+
+
+class P3B200Tables(ctypes.Structure):
+    _fields_ = [("mu_r_table_vals", ctypes.c_double * 150),
+                ("vn_table_vals", ctypes.c_double * 3000),
+                ("vm_table_vals", ctypes.c_double * 3000),
+                ("revap_table_vals", ctypes.c_double * 3000),
+                ("ice_table_vals", ctypes.c_double * 12000),
+                ("collect_table_vals", ctypes.c_double * 60000),
+                ("dnu_table_vals", ctypes.c_double * 16)]
+
+
+class P3B200Runtime(ctypes.Structure):
+    _fields_ = [(name, ctypes.c_double) for name, _ in RUNTIME_DEFAULTS[:-1]] + \
+               [("do_ice_production", ctypes.c_int32), ("pad_", ctypes.c_int32)]
+
+
+class P3B200Fields(ctypes.Structure):
+    _fields_ = [("ptr", ctypes.c_void_p * NUM_FIELDS), ("col_stride", ctypes.c_int64 * NUM_FIELDS)]
+
+
+class P3B200Infra(ctypes.Structure):
+    _fields_ = [("dt", ctypes.c_double), ("it", ctypes.c_int32), ("ncol", ctypes.c_int32),
+                ("nlev", ctypes.c_int32), ("predictNc", ctypes.c_int32), ("prescribedCCN", ctypes.c_int32),
+                ("zero_flux_top", ctypes.c_int32)]
+
+
+class P3Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def build(force=False):
+    """Compile libp3b200.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    csrc = os.path.join(PKG_DIR, "csrc")
+    if force:
+        subprocess.check_call(["make", "-C", csrc, "-s", "clean"])
+    subprocess.check_call(["make", "-C", csrc, "-s"])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise P3Error(f"{LIB_PATH} is missing: build it with `make -C scream_b200/csrc` "
+                          "(there is no CPU fallback for p3_main)")
+        L = ctypes.CDLL(LIB_PATH)
+        L.p3b200_strerror.restype = ctypes.c_char_p
+        L.p3b200_last_cuda_error.restype = ctypes.c_char_p
+        L.p3b200_runtime_defaults.restype = None
+        L.p3b200_create.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int, ctypes.c_int,
+                                    ctypes.POINTER(ctypes.c_void_p)]
+        L.p3b200_destroy.argtypes = [ctypes.c_void_p]
+        L.p3b200_main.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Runtime), ctypes.POINTER(P3B200Fields),
+                                  ctypes.POINTER(P3B200Infra), ctypes.c_void_p,
+                                  ctypes.POINTER(ctypes.c_int64), ctypes.c_void_p]
+        L.p3b200_main_host.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Runtime),
+                                       ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
+                                       ctypes.POINTER(ctypes.c_int64), ctypes.c_void_p]
+        L.p3b200_get_diag.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32]
+        L.p3b200_error_summary.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
+        L.p3b200_last_kernel_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
+                                            ctypes.POINTER(ctypes.c_int64)]
+        L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
+        L.p3b200_tables_read_text.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
+        L.p3b200_tables_read_blob.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
+        L.p3b200_tables_generate_rain.argtypes = [ctypes.POINTER(P3B200Tables)]
+        dp = ctypes.POINTER(ctypes.c_double)
+        L.p3b200_p3_main_f.argtypes = ([dp] * 6 + [ctypes.c_double] + [dp] * 10 + [ctypes.c_int] + [dp] * 2 +
+                                       [ctypes.c_int] * 4 + [dp] * 4 + [ctypes.c_int] * 2 + [dp] * 13)
+        _lib = L
+    return _lib
+
+
+def check(rc, what="p3b200"):
+    if rc != 0:
+        L = lib()
+        msg = L.p3b200_strerror(rc).decode()
+        cuda = L.p3b200_last_cuda_error().decode()
+        raise P3Error(f"{what} failed: {msg} (rc={rc}) {cuda}")
+
+
+_tables_cache = None
+
+
+def load_tables(blob=TABLE_BLOB, version=b"4.1.1"):
+    """Host-side P3LookupTables: ice/collection from the shipped blob, rain tables generated
+    (init_kokkos_ice_lookup_tables + init_kokkos_tables + p3_init_b)."""
+    global _tables_cache
+    if _tables_cache is None or blob != TABLE_BLOB:
+        t = P3B200Tables()
+        check(lib().p3b200_tables_read_blob(blob.encode(), version, ctypes.byref(t)), "tables_read_blob")
+        check(lib().p3b200_tables_generate_rain(ctypes.byref(t)), "tables_generate_rain")
+        if blob != TABLE_BLOB:
+            return t
+        _tables_cache = t
+    return _tables_cache
+
+
+def make_runtime(overrides=None):
+    r = P3B200Runtime()
+    lib().p3b200_runtime_defaults(ctypes.byref(r))
+    for k, v in (overrides or {}).items():
+        if k == "do_ice_production":
+            r.do_ice_production = int(bool(v))
+        else:
+            setattr(r, k, float(v))
+    return r
+
+
+def _levels(name, nlev):
+    return 1 if name in SURFACE_1D else (nlev + 1 if name in INTERFACE_FIELDS else nlev)
+
+
+class P3Handle:
+    """Owns one p3b200 handle (device tables + diagnostics) on one GPU."""
+
+    def __init__(self, device=0, real_bytes=8, tables=None):
+        self._h = ctypes.c_void_p()
+        self.real_bytes = real_bytes
+        self.device = device
+        t = tables if tables is not None else load_tables()
+        check(lib().p3b200_create(ctypes.byref(t), device, real_bytes, ctypes.byref(self._h)), "p3b200_create")
+
+    def close(self):
+        if self._h:
+            lib().p3b200_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- argument marshalling ------------------------------------------------------------------
+    def _infra(self, ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, it=1):
+        return P3B200Infra(float(dt), it, ncol, nlev, int(predict_nc), int(prescribed_ccn), int(zero_flux_top))
+
+    def fields_struct(self, fields, host):
+        """dict name -> (torch cuda tensor | numpy array), level index contiguous."""
+        f = P3B200Fields()
+        qc = fields["qc"]
+        ncol, nlev = qc.shape
+        for i, n in enumerate(FIELDS):
+            a = fields.get(n)
+            if a is None:
+                f.ptr[i] = None
+                f.col_stride[i] = 0
+                continue
+            if host:
+                assert a.dtype.itemsize == self.real_bytes, n
+                f.ptr[i] = a.ctypes.data
+                f.col_stride[i] = (a.strides[0] // self.real_bytes) if a.ndim == 2 else 1
+                if a.ndim == 2:
+                    assert a.strides[1] == self.real_bytes and a.shape == (ncol, _levels(n, nlev)), n
+            else:
+                assert a.is_cuda and a.element_size() == self.real_bytes, n
+                f.ptr[i] = a.data_ptr()
+                f.col_stride[i] = a.stride(0) if a.dim() == 2 else 1
+                if a.dim() == 2:
+                    assert a.stride(1) == 1 and tuple(a.shape) == (ncol, _levels(n, nlev)), n
+        return f, ncol, nlev
+
+    # ---- entry points --------------------------------------------------------------------------
+    def main(self, fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None, zero_flux_top=True,
+             stream=None, timed=False, diag=None):
+        """p3_main on device tensors, in place.  Returns device microseconds if timed else None."""
+        f, ncol, nlev = self.fields_struct(fields, host=False)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
+        us = ctypes.c_int64(0)
+        sptr = ctypes.c_void_p(stream) if stream else None
+        dptr = ctypes.c_void_p(diag.data_ptr()) if diag is not None else None
+        check(lib().p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+                                ctypes.byref(infra), sptr, ctypes.byref(us) if timed else None, dptr), "p3b200_main")
+        return us.value if timed else None
+
+    def main_prepared(self, f, infra, stream=None, runtime=None):
+        """Hot loop variant for benchmarks: pre-marshalled structs, asynchronous."""
+        check(lib().p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+                                ctypes.byref(infra), ctypes.c_void_p(stream) if stream else None, None, None),
+              "p3b200_main")
+
+    def main_host(self, fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None, zero_flux_top=True,
+                  want_diag=True):
+        """p3_main on host numpy arrays through the chunked H2D/kernel/D2H pipeline, in place."""
+        f, ncol, nlev = self.fields_struct(fields, host=True)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
+        us = ctypes.c_int64(0)
+        diag = np.full((ncol, NUM_DIAG), -7, dtype=np.int32) if want_diag else None
+        check(lib().p3b200_main_host(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+                                     ctypes.byref(infra), ctypes.byref(us),
+                                     diag.ctypes.data if want_diag else None), "p3b200_main_host")
+        return us.value, diag
+
+    def get_diag(self, ncol):
+        out = np.empty((ncol, NUM_DIAG), dtype=np.int32)
+        check(lib().p3b200_get_diag(self._h, out.ctypes.data, ncol), "p3b200_get_diag")
+        return out
+
+    def error_summary(self):
+        v = ctypes.c_int32(0)
+        check(lib().p3b200_error_summary(self._h, ctypes.byref(v)), "p3b200_error_summary")
+        return v.value
+
+    def last_kernel_ms(self):
+        ms = ctypes.c_double(0)
+        n = ctypes.c_int64(0)
+        check(lib().p3b200_last_kernel_ms(self._h, ctypes.byref(ms), ctypes.byref(n)), "p3b200_last_kernel_ms")
+        return ms.value, n.value
+
+
+def to_device(fields, device="cuda:0"):
+    import torch
+    return {n: torch.from_numpy(np.ascontiguousarray(v)).to(device) for n, v in fields.items()}
+
+
+def to_host(fields):
+    return {n: v.detach().cpu().numpy() for n, v in fields.items()}
