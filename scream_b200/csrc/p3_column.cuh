@@ -81,8 +81,9 @@ struct LaneBits {
   P3_HD bool get(int j) const { return (w[j >> 5] >> (j & 31)) & 1u; }
 };
 
-template <typename Real, typename WP>
+template <typename Real, typename WP, int JM_>
 struct Column {
+  static constexpr int JM = JM_;   // level slots per lane held in registers by sedimentation: JM*WP::size >= nk
   using P = Phys<Real>;
   using C = Cst<Real>;
   static constexpr int WS = WP::size;
@@ -91,22 +92,6 @@ struct Column {
   static P3_HD Real sp(double x) { return static_cast<Real>(x); }
 
   // ---------------------------------------------------------------------------------------------
-  // One upwind sub-step for field r with fall speed V over [k_top, k_bot_ext]
-  // (calc_first_order_upwind_step, p3_upwind_impl.hpp:18-91, kdir = -1: inflow from k-1).
-  static P3_HD void upwind_field(const WP& w, int lane, int k_top, int k_bot_ext, Real dt_sub,
-                                 const Real* V, Real* r, const ColumnSmem<Real>& s) {
-    for (int k = lane; k <= k_bot_ext; k += WS)
-      if (k >= k_top) s.flux[k] = V[k] * r[k] * s.rho[k];
-    w.sync();
-    for (int k = lane; k <= k_bot_ext; k += WS)
-      if (k >= k_top) {
-        const Real flux_above = (k == k_top) ? Real(0) : s.flux[k - 1];
-        const Real fluxdiv = (flux_above - s.flux[k]) * s.inv_dz[k];
-        r[k] += fluxdiv * dt_sub * (1 / s.rho[k]);
-      }
-    w.sync();
-  }
-
   // find_top / find_bottom (p3_find_impl.hpp:57-92, 17-52) for kdir = -1 over the whole column.
   static P3_HD bool find_range(const WP& w, int lane, int nk, const Real* q, int& k_top, int& k_bot) {
     int lo = MAX_NLEV + 1, hi = -1;
@@ -119,136 +104,208 @@ struct Column {
 
   enum { SP_CLOUD = 0, SP_RAIN = 1, SP_ICE = 2 };
 
+  // One first-order upwind sub-step of one field held in the register window
+  // (calc_first_order_upwind_step, p3_upwind_impl.hpp:18-91, kdir = -1: inflow from level k-1).
+  // Slot j of a lane holds level kw + lane + j*WS, so the level above lives in the previous lane of the
+  // same slot (one shuffle) or, for lane 0, in the last lane of the previous slot.  flux[] returns the
+  // fluxes of this field (needed for the surface accumulation and precip_liq_flux).
+  static P3_HD void upwind_window(const WP& w, int lane, int J, int kw, int k_temp, Real dt_sub,
+                                  const Real (&V)[JM], Real (&r)[JM], const Real (&rho)[JM],
+                                  const Real (&inv_rho)[JM], const Real (&inv_dz)[JM], Real (&flux)[JM]) {
+    Real prev_last = 0;
+#pragma unroll
+    for (int j = 0; j < JM; ++j) {
+      if (j < J) {
+        const int k = kw + lane + j * WS;
+        const bool in = k <= k_temp;
+        const Real f = in ? V[j] * r[j] * rho[j] : Real(0);
+        Real up = w.shfl_up1(f);
+        if (lane == 0) up = prev_last;
+        prev_last = w.shfl_from(f, WS - 1);
+        if (in) {
+          const Real fluxdiv = (up - f) * inv_dz[j];
+          r[j] += fluxdiv * dt_sub * inv_rho[j];
+        }
+        flux[j] = f;
+      }
+    }
+  }
+
   // cloud_sedimentation (p3_cloud_sed_impl.hpp:17-147), rain_sedimentation (p3_rain_sed_impl.hpp:39-170),
   // ice_sedimentation (p3_ice_sed_impl.hpp:69-205) share this CFL sub-step loop; SP selects the
-  // fall-speed physics.  In-cloud values are re-derived from the cell values: on the first sub-step
-  // they equal what calculate_incloud_mixingratios left at the end of part1/part2, afterwards q/cld_frac
-  // (the reference's end-of-sub-step refresh).
+  // fall-speed physics.
+  //
+  // Layout: the levels [k_qxtop, nk) that the hydrometeor can reach form a WINDOW anchored at k_qxtop;
+  // lane l keeps levels k_qxtop + l + j*WS (j = 0..J-1) entirely in registers for the whole sub-step
+  // loop (state, rho, 1/rho, 1/dz, cloud fraction, lazily evaluated density factor), slots being
+  // activated as the falling front (k_qxbot, +1 level per sub-step) reaches them.  A sub-step is then:
+  // fall speeds per lane, one warp max for the Courant number, and per field one shuffle for the
+  // inflow flux — no shared-memory round trips and no divisions that the reference does not have.
+  //
+  // In-cloud values are re-derived from the cell values: on the first sub-step they equal what
+  // calculate_incloud_mixingratios left at the end of part1/part2 (limits included), afterwards
+  // q/cld_frac (the reference's end-of-sub-step refresh).
   template <int SP>
   static P3_HD void sediment(const WP& w, int lane, const MainArgs<Real>& a, int64_t col,
                              const ColumnSmem<Real>& s, Real inv_dt, Real& surf_accum_out, int* dloc, int& err) {
     const int nk = a.nk, kbot = nk - 1;
     const Real qsmall = C::QSMALL;
-    Real* q = (SP == SP_CLOUD) ? s.qc : (SP == SP_RAIN) ? s.qr : s.qi;
-    Real* n = (SP == SP_CLOUD) ? s.nc : (SP == SP_RAIN) ? s.nr : s.ni;
+    Real* sq = (SP == SP_CLOUD) ? s.qc : (SP == SP_RAIN) ? s.qr : s.qi;
+    Real* sn = (SP == SP_CLOUD) ? s.nc : (SP == SP_RAIN) ? s.nr : s.ni;
     const int cf_id = (SP == SP_CLOUD) ? F_CLD_FRAC_L : (SP == SP_RAIN) ? F_CLD_FRAC_R : F_CLD_FRAC_I;
     const Real* cf_p = a.f[cf_id] + col * a.stride[cf_id];
     const Real* cfl_p = a.f[F_CLD_FRAC_L] + col * a.stride[F_CLD_FRAC_L];
+    Real* plf = a.f[F_PRECIP_LIQ_FLUX] + col * a.stride[F_PRECIP_LIQ_FLUX];
     int k_qxtop, k_qxbot;
-    const bool present = find_range(w, lane, nk, q, k_qxtop, k_qxbot);
+    const bool present = find_range(w, lane, nk, sq, k_qxtop, k_qxbot);
     const int dbase = (SP == SP_CLOUD) ? D_QC_KTOP : (SP == SP_RAIN) ? D_QR_KTOP : D_QI_KTOP;
     int nsub = 0;
     surf_accum_out = 0;
     if (!present) { dloc[dbase] = -1; dloc[dbase + 1] = -1; dloc[dbase + 2] = 0; return; }
 
-    if (SP != SP_CLOUD) {   // aux row becomes the lazily filled rhofacr / rhofaci cache
-      for (int k = lane; k < nk; k += WS) s.aux[k] = 0;
-    }
-    Real dt_left = a.dt, prt_accum = 0;
+    const int kw = k_qxtop;
+    Real q[JM], n[JM], qm[JM], bm[JM], rho[JM], inv_rho[JM], inv_dz[JM], cf[JM], fac[JM], acc[JM];
+    Real Vq[JM], Vn[JM], flux[JM], ftmp[JM];
+    int J = 0;                   // slots activated so far (warp-uniform)
+    Real dt_left = a.dt, prt_local = 0;
     bool first = true;
     while (dt_left > C::dt_left_tol) {
-      Real Co_loc = 0;
-      for (int k = lane; k < nk; k += WS) {
-        Real Vq = 0, Vn = 0;
-        if (k >= k_qxtop && k <= k_qxbot) {
-          const Real cf = P3_LDG(cf_p + k);
-          if (SP == SP_CLOUD) {
-            Real qc_i, nc_i;
-            if (first) P::incloud_liq(q[k], n[k], 1 / cf, qc_i, nc_i);
-            else { qc_i = q[k] / cf; nc_i = n[k] / cf; }
-            if (qc_i > qsmall) {
-              Real mu_c, lamc, d0, d1;
-              P::cloud_dsd2(qc_i, nc_i, s.rho[k], mu_c, lamc, d0, d1, false);
-              n[k] = nc_i * cf;
-              Real acn = s.aux[k];
-              if (acn > 0) {   // still T_atm(init): acn = g*rhow/(18*mu_air), p3_main_impl_part1.hpp:108-109
-                const Real dum = sp(1.496e-6) * std::pow(acn, sp(1.5)) / (acn + 120);
-                acn = -(C::gravit * C::RHO_H2O / (18 * dum));
-                s.aux[k] = acn;
-              }
-              acn = -acn;
-              const Real bcn = C::bcn;
-              const Real dum = 1 / std::pow(lamc, bcn);
-              Vq = acn * std::tgamma(4 + bcn + mu_c) * dum / std::tgamma(mu_c + 4);
-              if (a.predictNc) Vn = acn * std::tgamma(1 + bcn + mu_c) * dum / std::tgamma(mu_c + 1);
-              const Real Co = Vq * dt_left * s.inv_dz[k];
-              if (Co > Co_loc) Co_loc = Co;
-            }
-          } else if (SP == SP_RAIN) {
-            Real qr_i, nr_i;
-            if (first) P::incloud_rain(q[k], n[k], 1 / cf, qr_i, nr_i);
-            else { qr_i = q[k] / cf; nr_i = n[k] / cf; }
-            if (qr_i > qsmall) {
-              // compute_rain_fall_velocity: p3_rain_sed_impl.hpp:17-34
-              Real mu_r = 0, lamr;
-              P::rain_dsd2(qr_i, nr_i, mu_r, lamr, a.ro);
-              typename P::Loc3 t3;
-              P::lookup3(mu_r, lamr, t3);
-              Real rhofacr = s.aux[k];
-              if (rhofacr == 0) { rhofacr = std::pow(C::RHO_1000MB * (1 / s.rho[k]), sp(.54)); s.aux[k] = rhofacr; }
-              Vq = P::apply_table3(a.tb.vm, t3) * rhofacr;
-              Vn = P::apply_table3(a.tb.vn, t3) * rhofacr;
-              n[k] = nr_i * cf;
-              const Real Co = Vq * dt_left * s.inv_dz[k];
-              if (Co > Co_loc) Co_loc = Co;
-            }
+      const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
+      // activate the slots the front reaches in this sub-step
+      const int Jn = (k_temp - kw) / WS + 1;
+#pragma unroll
+      for (int j = 0; j < JM; ++j) {
+        if (j >= J && j < Jn) {
+          const int k = kw + lane + j * WS;
+          if (k < nk) {
+            q[j] = sq[k]; n[j] = sn[k];
+            if (SP == SP_ICE) { qm[j] = s.qm[k]; bm[j] = s.bm[k]; }
+            rho[j] = s.rho[k]; inv_rho[j] = 1 / rho[j]; inv_dz[j] = s.inv_dz[k];
+            cf[j] = P3_LDG(cf_p + k);
+            if (SP == SP_RAIN) acc[j] = plf[k + 1];
           } else {
-            Real qi_i, ni_i, qm_i, bm_i;
-            if (first) P::incloud_ice(q[k], n[k], s.qm[k], s.bm[k], 1 / cf, 1 / P3_LDG(cfl_p + k), qi_i, ni_i, qm_i, bm_i);
-            else { qi_i = q[k] / cf; ni_i = n[k] / cf; qm_i = s.qm[k] / cf; bm_i = s.bm[k] / cf; }
-            if (qi_i > qsmall) {
-              ni_i = P::rmax(ni_i, C::NSMALL);
-              const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
-              s.qm[k] = qm_i * cf;
-              s.bm[k] = bm_i * cf;
-              typename P::IceLoc ti;
-              P::lookup_ice(qi_i, ni_i, qm_i, rhop, ti);
-              const Real tv_ni_fallspd = P::apply_table_ice(0, a.tb.ice, ti);
-              const Real tv_qi_fallspd = P::apply_table_ice(1, a.tb.ice, ti);
-              const Real tv_ni_lammax  = P::apply_table_ice(6, a.tb.ice, ti);
-              const Real tv_ni_lammin  = P::apply_table_ice(7, a.tb.ice, ti);
-              ni_i = P::rmin(ni_i, tv_ni_lammax * ni_i);
-              ni_i = P::rmax(ni_i, tv_ni_lammin * ni_i);
-              n[k] = ni_i * cf;
-              Real rhofaci = s.aux[k];
-              if (rhofaci == 0) { rhofaci = std::pow(C::RHO_600MB * (1 / s.rho[k]), sp(.54)); s.aux[k] = rhofaci; }
-              Vq = a.ro.ice_sedimentation_factor * tv_qi_fallspd * rhofaci;
-              Vn = a.ro.ice_sedimentation_factor * tv_ni_fallspd * rhofaci;
-              const Real Co = Vq * dt_left * s.inv_dz[k];
-              if (Co > Co_loc) Co_loc = Co;
+            q[j] = 0; n[j] = 0; rho[j] = 1; inv_rho[j] = 1; inv_dz[j] = 0; cf[j] = 1;
+            if (SP == SP_ICE) { qm[j] = 0; bm[j] = 0; }
+            if (SP == SP_RAIN) acc[j] = 0;
+          }
+          fac[j] = 0;
+        }
+      }
+      if (Jn > J) J = Jn;
+
+      Real Co_loc = 0;
+#pragma unroll
+      for (int j = 0; j < JM; ++j) {
+        if (j < J) {
+          const int k = kw + lane + j * WS;
+          Real vq = 0, vn = 0;
+          if (k <= k_qxbot) {
+            if (SP == SP_CLOUD) {
+              Real qc_i, nc_i;
+              if (first) P::incloud_liq(q[j], n[j], 1 / cf[j], qc_i, nc_i);
+              else { qc_i = q[j] / cf[j]; nc_i = n[j] / cf[j]; }
+              if (qc_i > qsmall) {
+                Real mu_c, lamc, d0, d1;
+                P::cloud_dsd2(qc_i, nc_i, rho[j], mu_c, lamc, d0, d1, false);
+                n[j] = nc_i * cf[j];
+                if (fac[j] == 0) {   // acn = g*rhow/(18*mu_air(T_atm at init)), p3_main_impl_part1.hpp:108-109
+                  const Real T0 = s.aux[k];
+                  const Real dum = sp(1.496e-6) * std::pow(T0, sp(1.5)) / (T0 + 120);
+                  fac[j] = C::gravit * C::RHO_H2O / (18 * dum);
+                }
+                const Real acn = fac[j];
+                const Real bcn = C::bcn;
+                const Real dum = 1 / std::pow(lamc, bcn);
+                vq = acn * std::tgamma(4 + bcn + mu_c) * dum / std::tgamma(mu_c + 4);
+                if (a.predictNc) vn = acn * std::tgamma(1 + bcn + mu_c) * dum / std::tgamma(mu_c + 1);
+                const Real Co = vq * dt_left * inv_dz[j];
+                if (Co > Co_loc) Co_loc = Co;
+              }
+            } else if (SP == SP_RAIN) {
+              Real qr_i, nr_i;
+              if (first) P::incloud_rain(q[j], n[j], 1 / cf[j], qr_i, nr_i);
+              else { qr_i = q[j] / cf[j]; nr_i = n[j] / cf[j]; }
+              if (qr_i > qsmall) {
+                // compute_rain_fall_velocity: p3_rain_sed_impl.hpp:17-34
+                Real mu_r = 0, lamr;
+                P::rain_dsd2(qr_i, nr_i, mu_r, lamr, a.ro);
+                typename P::Loc3 t3;
+                P::lookup3(mu_r, lamr, t3);
+                if (fac[j] == 0) fac[j] = std::pow(C::RHO_1000MB * inv_rho[j], sp(.54));   // rhofacr
+                vq = P::apply_table3(a.tb.vm, t3) * fac[j];
+                vn = P::apply_table3(a.tb.vn, t3) * fac[j];
+                n[j] = nr_i * cf[j];
+                const Real Co = vq * dt_left * inv_dz[j];
+                if (Co > Co_loc) Co_loc = Co;
+              }
+            } else {
+              Real qi_i, ni_i, qm_i, bm_i;
+              if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], 1 / cf[j], 1 / P3_LDG(cfl_p + k), qi_i, ni_i, qm_i, bm_i);
+              else { qi_i = q[j] / cf[j]; ni_i = n[j] / cf[j]; qm_i = qm[j] / cf[j]; bm_i = bm[j] / cf[j]; }
+              if (qi_i > qsmall) {
+                ni_i = P::rmax(ni_i, C::NSMALL);
+                const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
+                qm[j] = qm_i * cf[j];
+                bm[j] = bm_i * cf[j];
+                typename P::IceLoc ti;
+                P::lookup_ice(qi_i, ni_i, qm_i, rhop, ti);
+                const Real tv_ni_fallspd = P::apply_table_ice(0, a.tb.ice, ti);
+                const Real tv_qi_fallspd = P::apply_table_ice(1, a.tb.ice, ti);
+                const Real tv_ni_lammax  = P::apply_table_ice(6, a.tb.ice, ti);
+                const Real tv_ni_lammin  = P::apply_table_ice(7, a.tb.ice, ti);
+                ni_i = P::rmin(ni_i, tv_ni_lammax * ni_i);
+                ni_i = P::rmax(ni_i, tv_ni_lammin * ni_i);
+                n[j] = ni_i * cf[j];
+                if (fac[j] == 0) fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54));     // rhofaci
+                vq = a.ro.ice_sedimentation_factor * tv_qi_fallspd * fac[j];
+                vn = a.ro.ice_sedimentation_factor * tv_ni_fallspd * fac[j];
+                const Real Co = vq * dt_left * inv_dz[j];
+                if (Co > Co_loc) Co_loc = Co;
+              }
             }
           }
+          Vq[j] = vq; Vn[j] = vn;
         }
-        s.Vq[k] = Vq;
-        s.Vn[k] = Vn;
       }
       const Real Co_max = w.max_real(Co_loc);
-      w.sync();
       // generalized_sedimentation: p3_upwind_impl.hpp:97-129
       if (!(Co_max >= 0)) err |= 4;
       const int tmpint1 = static_cast<int>(Co_max + 1);
       const Real dt_sub = dt_left / tmpint1;
-      const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
-      // fields are independent; the mass field goes last so that its flux row survives for
-      // prt_accum and precip_liq_flux.
       if (SP == SP_ICE) {
-        upwind_field(w, lane, k_qxtop, k_temp, dt_sub, s.Vq, s.bm, s);
-        upwind_field(w, lane, k_qxtop, k_temp, dt_sub, s.Vq, s.qm, s);
+        upwind_window(w, lane, J, kw, k_temp, dt_sub, Vq, bm, rho, inv_rho, inv_dz, ftmp);
+        upwind_window(w, lane, J, kw, k_temp, dt_sub, Vq, qm, rho, inv_rho, inv_dz, ftmp);
       }
-      if (SP != SP_CLOUD || a.predictNc) upwind_field(w, lane, k_qxtop, k_temp, dt_sub, s.Vn, n, s);
-      upwind_field(w, lane, k_qxtop, k_temp, dt_sub, s.Vq, q, s);
-      if (k_qxbot == kbot) prt_accum += s.flux[kbot] * dt_sub;
-      else k_qxbot += 1;
+      if (SP != SP_CLOUD || a.predictNc) upwind_window(w, lane, J, kw, k_temp, dt_sub, Vn, n, rho, inv_rho, inv_dz, ftmp);
+      upwind_window(w, lane, J, kw, k_temp, dt_sub, Vq, q, rho, inv_rho, inv_dz, flux);
+#pragma unroll
+      for (int j = 0; j < JM; ++j) {
+        if (j < J) {
+          const int k = kw + lane + j * WS;
+          if (k == kbot && k_qxbot == kbot) prt_local += flux[j] * dt_sub;
+          // precip_liq_flux(k+1) += flux_qx(k) for k in [k_qxtop, new k_qxbot], p3_rain_sed_impl.hpp:139-153
+          if (SP == SP_RAIN && k <= k_temp) acc[j] = acc[j] + flux[j];
+        }
+      }
+      if (k_qxbot != kbot) k_qxbot += 1;
       dt_left -= dt_sub;
-      if (SP == SP_RAIN) {   // precip_liq_flux(k+1) += flux_qx(k), p3_rain_sed_impl.hpp:139-153
-        Real* plf = a.f[F_PRECIP_LIQ_FLUX] + col * a.stride[F_PRECIP_LIQ_FLUX];
-        for (int k = lane; k <= k_qxbot + 1; k += WS)
-          if (k >= k_qxtop + 1) plf[k] = plf[k] + s.flux[k - 1];
-      }
-      w.sync();
       first = false;
       ++nsub;
     }
+    // write the window back
+#pragma unroll
+    for (int j = 0; j < JM; ++j) {
+      if (j < J) {
+        const int k = kw + lane + j * WS;
+        if (k < nk) {
+          sq[k] = q[j]; sn[k] = n[j];
+          if (SP == SP_ICE) { s.qm[k] = qm[j]; s.bm[k] = bm[j]; }
+          if (SP == SP_RAIN) plf[k + 1] = acc[j];
+        }
+      }
+    }
+    w.sync();
+    const Real prt_accum = w.shfl_from(prt_local, (kbot - kw) % WS);   // only the lane owning kbot accumulated
     surf_accum_out = prt_accum * C::INV_RHO_H2O * inv_dt;
     dloc[dbase] = k_qxtop; dloc[dbase + 1] = k_qxbot; dloc[dbase + 2] = nsub;
   }

@@ -34,9 +34,12 @@ struct WarpDev {
   __device__ __forceinline__ int max_int(int v) const { return __reduce_max_sync(FULL, v); }
   __device__ __forceinline__ int or_int(int v) const { return (int)__reduce_or_sync(FULL, (unsigned)v); }
   __device__ __forceinline__ void sync() const { __syncwarp(); }
+  // value of the previous lane (lane 0 keeps its own: callers patch it) / of lane `src`
+  template <class R> __device__ __forceinline__ R shfl_up1(R v) const { return __shfl_up_sync(FULL, v, 1); }
+  template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
 };
 
-template <typename Real>
+template <typename Real, int JM>
 __global__ void __launch_bounds__(128)
 p3_main_kernel(const __grid_constant__ MainArgs<Real> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -49,30 +52,22 @@ p3_main_kernel(const __grid_constant__ MainArgs<Real> a) {
     if (lane == 0) col = atomicAdd(a.queue, 1u);
     col = __shfl_sync(WarpDev::FULL, col, 0);
     if (col >= (unsigned)a.ncol) break;
-    Column<Real, WarpDev>::run(w, a, (int64_t)col, smem);
+    Column<Real, WarpDev, JM>::run(w, a, (int64_t)col, smem);
   }
 }
 
-template <typename Real>
-int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
-  int dev = 0, sms = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (e != cudaSuccess) return (int)e;
-  int max_optin = 0;
-  e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  if (e != cudaSuccess) return (int)e;
+template <typename Real, int JM>
+static int plan_for(int nk, int ncol, int sms, int max_optin, LaunchConfig* cfg) {
   const int per_warp = NUM_SMEM_ROWS * nk * (int)sizeof(Real);
   int wpb = 4;
   while (wpb > 1 && wpb * per_warp > max_optin) wpb >>= 1;
   if (wpb * per_warp > max_optin) return (int)cudaErrorInvalidValue;
   cfg->warps_per_block = wpb;
   cfg->smem_bytes = wpb * per_warp;
-  e = cudaFuncSetAttribute(p3_main_kernel<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg->smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(p3_main_kernel<Real, JM>, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg->smem_bytes);
   if (e != cudaSuccess) return (int)e;
   int bps = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, p3_main_kernel<Real>, wpb * 32, cfg->smem_bytes);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, p3_main_kernel<Real, JM>, wpb * 32, cfg->smem_bytes);
   if (e != cudaSuccess) return (int)e;
   if (bps < 1) return (int)cudaErrorLaunchOutOfResources;
   cfg->blocks_per_sm = bps;
@@ -84,9 +79,27 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
   return 0;
 }
 
+// Two instantiations per precision: JM = 4 register slots per lane (nk <= 128, the production grids)
+// and JM = 8 (nk <= 256).
+template <typename Real>
+int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
+  int dev = 0, sms = 0, max_optin = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return (int)e;
+  if (nk > MAX_NLEV) return (int)cudaErrorInvalidValue;
+  return nk <= 128 ? plan_for<Real, 4>(nk, ncol, sms, max_optin, cfg) : plan_for<Real, 8>(nk, ncol, sms, max_optin, cfg);
+}
+
 template <typename Real>
 int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream) {
-  p3_main_kernel<Real><<<cfg.blocks, cfg.warps_per_block * 32, cfg.smem_bytes, (cudaStream_t)stream>>>(a);
+  if (a.nk <= 128)
+    p3_main_kernel<Real, 4><<<cfg.blocks, cfg.warps_per_block * 32, cfg.smem_bytes, (cudaStream_t)stream>>>(a);
+  else
+    p3_main_kernel<Real, 8><<<cfg.blocks, cfg.warps_per_block * 32, cfg.smem_bytes, (cudaStream_t)stream>>>(a);
   return (int)cudaGetLastError();
 }
 

@@ -18,6 +18,8 @@ struct WarpSim {
   int max_int(int v) const { return v; }
   int or_int(int v) const { return v; }
   void sync() const {}
+  template <class R> R shfl_up1(R v) const { return v; }
+  template <class R> R shfl_from(R v, int) const { return v; }
 };
 
 template <typename Real>
@@ -42,7 +44,7 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   a.diag = diag; a.queue = nullptr;
   std::vector<Real> smem(size_t(NUM_SMEM_ROWS) * nlev);
   WarpSim w;
-  for (int i = 0; i < ncol; ++i) Column<Real, WarpSim>::run(w, a, i, smem.data());
+  for (int i = 0; i < ncol; ++i) Column<Real, WarpSim, p3b200::MAX_NLEV>::run(w, a, i, smem.data());
   return 0;
 }
 }  // namespace
