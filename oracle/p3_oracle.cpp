@@ -156,12 +156,13 @@ void p3o_gen_rain_tables(double* vn, double* vm, double* revap, double* mu_r_tab
         else if (dia*1.e+6 < 1511.64)  vt = 4.962e+1*std::pow(amg, thrd);
         else if (dia*1.e+6 < 3477.84)  vt = 1.732e+1*std::pow(amg, sxth);
         else                           vt = 9.17;
-        const double e = std::exp(-lamr*dia)*dd*1.e-6;
-        dum1 += vt*std::pow(10., mu_r*std::log10(dia)+4.*mu_r)*e;
-        dum2 += std::pow(10., mu_r*std::log10(dia)+4.*mu_r)*e;
-        dum3 += vt*std::pow(10., (mu_r+3.)*std::log10(dia)+4.*mu_r)*e;
-        dum4 += std::pow(10., (mu_r+3.)*std::log10(dia)+4.*mu_r)*e;
-        dum5 += std::pow(vt*dia, 0.5)*std::pow(10., (mu_r+1.)*std::log10(dia)+3.*mu_r)*e;
+        // left-to-right like the Fortran expression: ((vt*10**x)*exp(..))*dd*1e-6  (F90:321-325)
+        const double ex = std::exp(-lamr*dia);
+        dum1 = dum1 + vt*std::pow(10., mu_r*std::log10(dia)+4.*mu_r)*ex*dd*1.e-6;
+        dum2 = dum2 + std::pow(10., mu_r*std::log10(dia)+4.*mu_r)*ex*dd*1.e-6;
+        dum3 = dum3 + vt*std::pow(10., (mu_r+3.)*std::log10(dia)+4.*mu_r)*ex*dd*1.e-6;
+        dum4 = dum4 + std::pow(10., (mu_r+3.)*std::log10(dia)+4.*mu_r)*ex*dd*1.e-6;
+        dum5 = dum5 + std::pow(vt*dia, 0.5)*std::pow(10., (mu_r+1.)*std::log10(dia)+3.*mu_r)*ex*dd*1.e-6;
       }
       dum2 = std::max(dum2, 1.e-30);
       dum4 = std::max(dum4, 1.e-30);

@@ -1,0 +1,73 @@
+"""CPU checks of the product's column-driver SOURCE (p3_column.cuh / p3_physics.cuh) against the oracle.
+
+The same headers the sm_100a kernel instantiates are compiled for the host with a 1-lane warp
+(tests/hostsim).  These tests prove the driver logic (fusion of init/part1/part2, deferred history
+stores, register-window sedimentation, lazy density factors, host-precomputed gamma values) without
+a GPU; the GPU parity tests proper are in test_gpu_parity.py.
+"""
+import numpy as np
+import pytest
+
+from scream_b200 import ic_cases
+from tests import hostsim_lib, parity
+
+FLAGS = [(False, False), (False, True), (True, False), (True, True)]
+
+
+def _pair(oracle, f, dt, predict_nc, prescribed_ccn, nsteps=1):
+    ref, got = parity.clone(f), parity.clone(f)
+    d_ref = d_got = None
+    for _ in range(nsteps):
+        parity.zero_outputs(ref)
+        parity.zero_outputs(got)
+        _, d_ref = oracle.p3_main(ref, dt, predict_nc, prescribed_ccn)
+        d_got = hostsim_lib.p3_main(got, dt, predict_nc, prescribed_ccn)
+    return ref, got, d_ref, d_got
+
+
+@pytest.mark.parametrize("predict_nc,prescribed_ccn", FLAGS)
+@pytest.mark.parametrize("dtype,nsteps,tol", [(np.float64, 1, 1e-14), (np.float32, 1, 1e-6),
+                                              (np.float64, 6, 1e-9), (np.float32, 6, 1e-3)])
+def test_mixed_ic(oracle, dtype, nsteps, tol, predict_nc, prescribed_ccn):
+    """p3_run_and_cmp protocol (p3_run_and_cmp.cpp:218-352): mixed(3,72), dt=300, 1 and 6 steps.
+    One step: rounding-level agreement.  Six steps: last-bit differences (the driver reuses shared
+    sub-expressions) pass through the threshold cascade, hence the looser multi-step bound."""
+    f = ic_cases.make_mixed(3, 72, dtype)
+    ref, got, d_ref, d_got = _pair(oracle, f, 300.0, predict_nc, prescribed_ccn, nsteps=nsteps)
+    errs = parity.field_errors(ref, got)
+    assert max(errs.values()) <= tol, {k: v for k, v in errs.items() if v > tol}
+    assert np.array_equal(d_ref, d_got)
+
+
+@pytest.mark.parametrize("nlev,dt", [(72, 1800.0), (128, 300.0), (33, 300.0), (200, 100.0)])
+def test_random_columns(oracle, nlev, dt):
+    """G2 random cloud layers, incl. a ragged level count and nlev > 128 (8 slots per lane)."""
+    f = ic_cases.make_random(768, nlev)
+    ref, got, d_ref, d_got = _pair(oracle, f, dt, True, True)
+    bad = parity.column_mismatch(ref, got, 1e-13)
+    assert not bad.any(), f"{bad.sum()} columns differ"
+    assert np.array_equal(d_ref, d_got)
+
+
+def test_clear_sky_early_exit(oracle):
+    """Columns with no hydrometeors and no nucleation leave after part1 (p3_main_impl.hpp:237):
+    defaults for the effective radii, history arrays untouched, zero precipitation."""
+    f = ic_cases.make_mixed(4, 72)
+    for n in ("qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm"):
+        f[n][...] = 0
+    f["qv"][...] = 1e-7
+    f["th"][...] = 300.0 * f["inv_exner"]      # warm: no nucleation possible
+    ref, got, d_ref, d_got = _pair(oracle, f, 300.0, True, True)
+    assert (d_ref[:, :2] == 0).all()
+    assert np.array_equal(d_ref, d_got)
+    for n in parity.OUTPUTS:
+        assert np.array_equal(ref[n], got[n]), n
+    assert (got["diag_eff_radius_qc"] == 10e-6).all() and (got["precip_liq_surf"] == 0).all()
+
+
+def test_single_level_and_single_column(oracle):
+    f = ic_cases.make_random(1, 1)
+    ref, got, d_ref, d_got = _pair(oracle, f, 300.0, True, True)
+    for n in parity.OUTPUTS:
+        np.testing.assert_allclose(got[n], ref[n], rtol=1e-13, atol=0, err_msg=n)
+    assert np.array_equal(d_ref, d_got)
