@@ -161,7 +161,7 @@ int p3b200_destroy(p3b200_handle h);
 
 /* p3_main on DEVICE arrays.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = default stream)
  * unless elapsed_us != NULL, in which case it synchronises and returns the device time of the
- * launch in microseconds like p3_main does (p3_main_impl.hpp:105,326-330).
+ * five launches in microseconds like p3_main does (p3_main_impl.hpp:105,326-330).
  * diag_dev: optional device int32[ncol*P3B200_D_NUM]; NULL = keep them in the handle
  * (p3b200_get_diag). */
 int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
@@ -181,6 +181,9 @@ int p3b200_main_host(p3b200_handle h, const P3B200Runtime* runtime, const P3B200
 /* Device kernel time (ms) of the last p3b200_main/p3b200_main_host measured with CUDA events on the
  * launching stream(s) (sum over chunks); synchronises. */
 int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches);
+/* The same split by launch: ms5[0] phase A (init+part1+part2), ms5[1..3] cloud/rain/ice sedimentation,
+ * ms5[4] phase C (homogeneous freezing + part3); each summed over the chunks of the last call. */
+int p3b200_last_phase_ms(p3b200_handle h, double* ms5);
 
 /* ---- the reference's own C bridge, re-implemented on the GPU ---------------------------------------
  * Drop-in for p3_main_f (p3_functions_f90.hpp:945-952; p3_functions_f90.cpp:1888-2103): HOST pointers,

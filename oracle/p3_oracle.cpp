@@ -14,6 +14,8 @@
 
 using namespace p3o;
 
+double p3o::pm::g_scale[p3o::pm::NUM_FN] = {1, 1, 1, 1, 1, 1, 1, 1};
+
 namespace {
 
 // Field order shared by the oracle and the product C ABI (include/p3_b200.h, P3B200_F_*).
@@ -235,3 +237,10 @@ double p3o_main(void* tables, int real_bytes, void* const* fields, const int64_t
 }
 
 } // extern "C"
+
+// Conditioning probe: relative scale applied to the result of pow, exp, log, log10, cbrt, tgamma,
+// tanh, expm1 (in this order).  nullptr restores the exact libm values.  Not thread safe: call between runs.
+extern "C" void p3o_set_math_scale(const double* scale8) {
+  for (int i = 0; i < p3o::pm::NUM_FN; ++i) p3o::pm::g_scale[i] = scale8 ? scale8[i] : 1.0;
+}
+

@@ -92,9 +92,9 @@ struct Main {
       w.qv_sat_l[k] = P::qv_sat_dry(w.T_atm[k], c.pres[k], false, err);
       w.qv_sat_i[k] = P::qv_sat_dry(w.T_atm[k], c.pres[k], true,  err);
       w.qv_supersat_i[k] = c.qv[k] / w.qv_sat_i[k] - 1;
-      w.rhofacr[k] = std::pow(rho_1000mb * w.inv_rho[k], sp(.54));
-      w.rhofaci[k] = std::pow(rho_600mb * w.inv_rho[k], sp(.54));
-      const Real dum = sp(1.496e-6) * std::pow(w.T_atm[k], sp(1.5)) / (w.T_atm[k] + 120);
+      w.rhofacr[k] = pm::pow(rho_1000mb * w.inv_rho[k], sp(.54));
+      w.rhofaci[k] = pm::pow(rho_600mb * w.inv_rho[k], sp(.54));
+      const Real dum = sp(1.496e-6) * pm::pow(w.T_atm[k], sp(1.5)) / (w.T_atm[k] + 120);
       w.acn[k] = g * rho_h2o / (18 * dum);
       if (w.T_atm[k] < T_zerodegc && w.qv_supersat_i[k] >= sp(-0.05)) nucleationPossible = true;
 
@@ -403,10 +403,10 @@ struct Main {
             Real nu, cdist, cdist1;
             P::get_cloud_dsd2(w.qc_incld[k], w.nc_incld[k], w.mu_c[k], w.rho[k], nu, w.lamc[k], cdist, cdist1);
             c.nc[k] = w.nc_incld[k]*c.cld_frac_l[k];
-            const Real dum = 1 / std::pow(w.lamc[k], bcn);
-            w.V_q[k] = w.acn[k]*std::tgamma(4 + bcn + w.mu_c[k]) * dum / std::tgamma(w.mu_c[k]+4);
+            const Real dum = 1 / pm::pow(w.lamc[k], bcn);
+            w.V_q[k] = w.acn[k]*pm::tgamma(4 + bcn + w.mu_c[k]) * dum / pm::tgamma(w.mu_c[k]+4);
             if (do_predict_nc)
-              w.V_n[k] = w.acn[k]*std::tgamma(1 + bcn + w.mu_c[k]) * dum / std::tgamma(w.mu_c[k]+1);
+              w.V_n[k] = w.acn[k]*pm::tgamma(1 + bcn + w.mu_c[k]) * dum / pm::tgamma(w.mu_c[k]+1);
             const Real Co_max_local = w.V_q[k] * dt_left * w.inv_dz[k];
             if (Co_max_local > Co_max) Co_max = Co_max_local;
           }
@@ -611,7 +611,7 @@ struct Main {
           P::get_rain_dsd2(qr_incld, nr_incld, w.mu_r[k], w.lamr[k], ro);
           c.nr[k] = nr_incld*c.cld_frac_r[k];
           w.ze_rain[k] = c.nr[k]*(w.mu_r[k]+6)*(w.mu_r[k]+5)*(w.mu_r[k]+4)*
-                         (w.mu_r[k]+3)*(w.mu_r[k]+2)*(w.mu_r[k]+1)/std::pow(w.lamr[k], sp(6.0));
+                         (w.mu_r[k]+3)*(w.mu_r[k]+2)*(w.mu_r[k]+1)/pm::pow(w.lamr[k], sp(6.0));
           w.ze_rain[k] = P::max(w.ze_rain[k], sp(1.e-22));
           c.diag_eff_radius_qr[k] = sp(1.5) / w.lamr[k];
         } else {
@@ -666,7 +666,7 @@ struct Main {
           w.diag_diam_qi[k] = 0;
         }
       }
-      w.diag_equiv_reflectivity[k] = 10 * std::log10((w.ze_rain[k] + w.ze_ice[k])*sp(1.e18));
+      w.diag_equiv_reflectivity[k] = 10 * pm::log10((w.ze_rain[k] + w.ze_ice[k])*sp(1.e18));
       if (c.qr[k] < qsmall) c.nr[k] = 0;
     }
   }

@@ -39,13 +39,13 @@ struct Procs {
     const bool ice_mask = (t_atm < tmelt) && ice;
     if (ice_mask) {
       const Real ic[] = {sp(9.550426), sp(5723.265), sp(3.53068), sp(0.00728332)};
-      result = std::exp(ic[0] - (ic[1] / t_atm) + (ic[2] * std::log(t_atm)) - (ic[3] * t_atm));
+      result = pm::exp(ic[0] - (ic[1] / t_atm) + (ic[2] * pm::log(t_atm)) - (ic[3] * t_atm));
     } else {
       const Real lq[] = {sp(54.842763), sp(6763.22), sp(4.210), sp(0.000367), sp(0.0415), sp(218.8),
                          sp(53.878), sp(1331.22), sp(9.44523), sp(0.014025)};
-      const Real logt = std::log(t_atm);
-      result = std::exp(lq[0] - (lq[1] / t_atm) - (lq[2] * logt) + (lq[3] * t_atm) +
-                        (std::tanh(lq[4] * (t_atm - lq[5])) * (lq[6] - (lq[7] / t_atm) -
+      const Real logt = pm::log(t_atm);
+      result = pm::exp(lq[0] - (lq[1] / t_atm) - (lq[2] * logt) + (lq[3] * t_atm) +
+                        (pm::tanh(lq[4] * (t_atm - lq[5])) * (lq[6] - (lq[7] / t_atm) -
                                                              (lq[8] * logt) + lq[9] * t_atm)));
     }
     return result;
@@ -85,8 +85,8 @@ struct Procs {
   static void get_time_space_phys_variables(
       Real T_atm, Real pres, Real rho, Real qv_sat_l, Real qv_sat_i,
       Real& mu, Real& dv, Real& sc, Real& dqsdt, Real& dqsidt, Real& ab, Real& abi, Real& kap, Real& eii) {
-    mu = sp(1.496e-6) * std::pow(T_atm, sp(1.5))/(T_atm+120);
-    dv = sp(8.794e-5) * std::pow(T_atm, sp(1.81))/pres;
+    mu = sp(1.496e-6) * pm::pow(T_atm, sp(1.5))/(T_atm+120);
+    dv = sp(8.794e-5) * pm::pow(T_atm, sp(1.81))/pres;
     sc = mu/(rho*dv);
     const Real RV = C::RV, INV_CP = C::INV_CP, latvap = C::LatVap, latice = C::LatIce;
     const Real tval1 = 253.15, tval2 = 273.15, dtval = 20;
@@ -114,7 +114,7 @@ struct Procs {
       mu_c_local = max(mu_c_local, 2);
       mu_c_local = min(mu_c_local, 15);
       mu_c = mu_c_local;
-      lamc = std::cbrt(cons1 * nc * (mu_c + 3) * (mu_c + 2) * (mu_c + 1) / qc);
+      lamc = pm::cbrt(cons1 * nc * (mu_c + 3) * (mu_c + 2) * (mu_c + 1) / qc);
       const Real lammin = (mu_c + 1)*sp(2.5e+4);
       const Real lammax = (mu_c + 1)*sp(1.e+6);
       const bool lamc_lt_min = lamc < lammin, lamc_gt_max = lamc > lammax;
@@ -123,7 +123,7 @@ struct Procs {
       if (lamc_lt_min || lamc_gt_max)
         nc = 6 * (lamc * lamc * lamc) * qc / (C::Pi * C::RHO_H2O * (mu_c + 3) * (mu_c + 2) * (mu_c + 1));
       cdist  = nc * (mu_c+1) / lamc;
-      cdist1 = nc / std::tgamma(mu_c + 1);
+      cdist1 = nc / pm::tgamma(mu_c + 1);
     }
   }
 
@@ -136,7 +136,7 @@ struct Procs {
       const Real nr_lim = max(nr, nsmall);
       mu_r = mu_r_const;
       const Real mass_to_d3_factor = cons1 * (mu_r + 3) * (mu_r + 2) * (mu_r + 1);
-      lamr = std::cbrt(mass_to_d3_factor * nr_lim / qr);
+      lamr = pm::cbrt(mass_to_d3_factor * nr_lim / qr);
       const Real lammax = (mu_r+sp(1.))*sp(1.e+5);
       const Real lammin = (mu_r+sp(1.))*500;
       const bool lt = lamr < lammin, gt = lamr > lammax;
@@ -153,8 +153,8 @@ struct Procs {
   static void get_cdistr_logn0r(Real qr, Real nr, Real mu_r, Real lamr, Real& cdistr, Real& logn0r) {
     cdistr = 0; logn0r = 0;
     if (qr >= C::QSMALL) {
-      cdistr = nr/std::tgamma(mu_r + 1);
-      logn0r = std::log10(cdistr) + (mu_r + 1) * std::log10(lamr);
+      cdistr = nr/pm::tgamma(mu_r + 1);
+      logn0r = pm::log10(cdistr) + (mu_r + 1) * pm::log10(lamr);
     }
   }
 
@@ -186,7 +186,7 @@ struct Procs {
   // p3_table_ice_impl.hpp:83-138
   static void lookup_ice(Real qi, Real ni, Real qm, Real rhop, TableIce<Real>& tab) {
     const Real c = static_cast<Real>(P3C::lookup_table_1a_dum1_c);
-    tab.dum1 = (std::log10(qi/ni)+18) * c - 10;
+    tab.dum1 = (pm::log10(qi/ni)+18) * c - 10;
     tab.dumi = static_cast<int>(tab.dum1);
     tab.dum1 = min(tab.dum1, static_cast<Real>(P3C::isize));
     tab.dum1 = max(tab.dum1, sp(1.));
@@ -215,8 +215,8 @@ struct Procs {
     const Real qsmall = C::QSMALL;
     const bool gt_small = qr > qsmall && nr > 0.0;
     Real dumlr = 1;
-    if (gt_small) dumlr = std::cbrt(qr/(C::Pi * C::RHO_H2O * nr));
-    tab.dum3 = (std::log10(1*dumlr) + 5)*sp(10.70415);
+    if (gt_small) dumlr = pm::cbrt(qr/(C::Pi * C::RHO_H2O * nr));
+    tab.dum3 = (pm::log10(1*dumlr) + 5)*sp(10.70415);
     tab.dumj = static_cast<int>(tab.dum3);
     tab.dum3 = min(tab.dum3, static_cast<Real>(P3C::rcollsize));
     tab.dum3 = max(tab.dum3, 1);
@@ -336,11 +336,11 @@ struct Procs {
     const Real ten = 10.0;
     const Real f = ro.rain_to_ice_collection_factor;
     if (both_ge_small && t_is_negative) {
-      qr2qi_collect_tend = std::pow(ten, table_val_qr2qi_collect + logn0r) * rho * rhofaci * f * ni_incld;
-      nr_collect_tend    = std::pow(ten, table_val_nr_collect + logn0r) * rho * rhofaci * f * ni_incld;
+      qr2qi_collect_tend = pm::pow(ten, table_val_qr2qi_collect + logn0r) * rho * rhofaci * f * ni_incld;
+      nr_collect_tend    = pm::pow(ten, table_val_nr_collect + logn0r) * rho * rhofaci * f * ni_incld;
     }
     if (both_ge_small && !t_is_negative)
-      nr_collect_tend    = std::pow(ten, table_val_nr_collect + logn0r) * rho * rhofaci * f * ni_incld;
+      nr_collect_tend    = pm::pow(ten, table_val_nr_collect + logn0r) * rho * rhofaci * f * ni_incld;
   }
 
   // p3_ice_collection_impl.hpp:107-153
@@ -368,7 +368,7 @@ struct Procs {
     const bool has_melt_qi = (qi_incld >= QSMALL) && (T_atm > Tmelt);
     if (has_melt_qi) {
       const Real qsat0 = qv_sat_dry(Tmelt, pres, false, err);
-      qi2qr_melt_tend = ( (table_val_qi2qr_melting+table_val_qi2qr_vent_melt*std::cbrt(sc)*std::sqrt(rhofaci*rho/mu))
+      qi2qr_melt_tend = ( (table_val_qi2qr_melting+table_val_qi2qr_vent_melt*pm::cbrt(sc)*std::sqrt(rhofaci*rho/mu))
                           *((T_atm-Tmelt)*kap-rho*latvap*dv*(qsat0-qv))
                           * 2 * Pi /latice)*ni_incld;
       qi2qr_melt_tend = max(qi2qr_melt_tend, 0);
@@ -388,7 +388,7 @@ struct Procs {
     const bool any_if_col = any_if && (qc2qi_collect_tend + qr2qi_collect_tend) >= sp(1.0e-10);
     if (any_if) {
       const Real qsat0 = qv_sat_dry(tmelt, pres, false, err);
-      qc_growth_rate = ((table_val_qi2qr_melting+table_val_qi2qr_vent_melt*std::cbrt(sc)*std::sqrt(rhofaci*rho/mu))*
+      qc_growth_rate = ((table_val_qi2qr_melting+table_val_qi2qr_vent_melt*pm::cbrt(sc)*std::sqrt(rhofaci*rho/mu))*
                         twopi*(rho*latvap*dv*(qsat0-qv)-(temp-tmelt)*kap)/
                         (latice+cpw*(temp-tmelt)))*ni_incld;
       qc_growth_rate = max(qc_growth_rate, zero);
@@ -417,7 +417,7 @@ struct Procs {
     const Real qsmall = C::QSMALL, tmelt = C::Tmelt, pi = C::Pi;
     const bool any_if = qi_incld >= qsmall && temp < tmelt;
     if (any_if) {
-      epsi = ((table_val_qi2qr_melting+table_val_qi2qr_vent_melt*std::cbrt(sc)*std::sqrt(rhofaci*rho/mu))*
+      epsi = ((table_val_qi2qr_melting+table_val_qi2qr_vent_melt*pm::cbrt(sc)*std::sqrt(rhofaci*rho/mu))*
               sp(2.0)*pi*rho*dv)*ni_incld;
       epsi_tot = epsi_tot+epsi;
     } else {
@@ -433,7 +433,7 @@ struct Procs {
     if (m) {
       vtrmi1 = table_val_qi_fallspd * rhofaci;
       if (qc_incld >= qsmall) {
-        const Real Vt_qc = acn * std::tgamma(4+bcn+mu_c) / (std::pow(lamc, bcn) * std::tgamma(4+mu_c));
+        const Real Vt_qc = acn * pm::tgamma(4+bcn+mu_c) / (pm::pow(lamc, bcn) * pm::tgamma(4+mu_c));
         const Real D_c = (4 + mu_c) / lamc;
         const Real V_impact = std::abs(vtrmi1-Vt_qc);
         const Real inv_Tc = 1/min(sp(-0.001), T_atm-T_zerodegc);
@@ -456,11 +456,11 @@ struct Procs {
     const Real qsmall = C::QSMALL, T_rainfrz = C::T_rainfrz, T_zerodegc = C::T_zerodegc;
     const Real CONS5 = C::CONS5, CONS6 = C::CONS6;
     if ((qc_incld >= qsmall) && (T_atm <= T_rainfrz)) {
-      const Real expAimmDt = std::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
+      const Real expAimmDt = pm::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
       const Real inv_lamc3 = cube(1/lamc);
       const Real sgs_var_coef = 1;
-      qc2qi_hetero_freeze_tend = sgs_var_coef * CONS6 * cdist1 * std::tgamma(7+mu_c) * expAimmDt * square(inv_lamc3);
-      nc2ni_immers_freeze_tend = CONS5 * cdist1 * std::tgamma(sp(4.0)+mu_c) * expAimmDt * inv_lamc3;
+      qc2qi_hetero_freeze_tend = sgs_var_coef * CONS6 * cdist1 * pm::tgamma(7+mu_c) * expAimmDt * square(inv_lamc3);
+      nc2ni_immers_freeze_tend = CONS5 * cdist1 * pm::tgamma(sp(4.0)+mu_c) * expAimmDt * inv_lamc3;
     }
   }
 
@@ -471,11 +471,11 @@ struct Procs {
     const Real CONS5 = C::CONS5, CONS6 = C::CONS6;
     if ((qr_incld >= qsmall) && (T_atm <= T_rainfrz)) {
       qr2qi_immers_freeze_tend = CONS6 *
-          std::exp(std::log(cdistr) + std::log(std::tgamma(sp(7.) + mu_r)) - sp(6.) * std::log(lamr)) *
-          std::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
+          pm::exp(pm::log(cdistr) + pm::log(pm::tgamma(sp(7.) + mu_r)) - sp(6.) * pm::log(lamr)) *
+          pm::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
       nr2ni_immers_freeze_tend = CONS5 *
-          std::exp(std::log(cdistr) + std::log(std::tgamma(sp(4.) + mu_r)) - sp(3.) * std::log(lamr)) *
-          std::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
+          pm::exp(pm::log(cdistr) + pm::log(pm::tgamma(sp(4.) + mu_r)) - sp(3.) * pm::log(lamr)) *
+          pm::exp(ro.immersion_freezing_exponent * (T_zerodegc - T_atm));
     }
   }
 
@@ -489,15 +489,15 @@ struct Procs {
       Table3<Real> table;
       lookup(mu_r, lamr, table);
       epsr = 2 * pi * cdistr * rho * dv *
-             (f1r * std::tgamma(mu_r + 2)/lamr +
-              f2r * std::sqrt(rho/mu) * std::cbrt(sc) * apply_table(t.revap_table_vals, table));
+             (f1r * pm::tgamma(mu_r + 2)/lamr +
+              f2r * std::sqrt(rho/mu) * pm::cbrt(sc) * apply_table(t.revap_table_vals, table));
     }
     if (qc_incld >= qsmall) epsc = 2 * pi * rho * dv * cdist;
     else                    epsc = 0;
   }
 
   // p3_evaporate_rain_impl.hpp:13-64
-  static Real rain_evap_tscale_weight(Real dt_over_tau) { return -std::expm1(-dt_over_tau)/dt_over_tau; }
+  static Real rain_evap_tscale_weight(Real dt_over_tau) { return -pm::expm1(-dt_over_tau)/dt_over_tau; }
   static Real rain_evap_equilib_tend(Real A_c, Real ab, Real tau_eff, Real tau_r) { return -A_c/ab*tau_eff/tau_r; }
   static Real rain_evap_instant_tend(Real ssat_r, Real ab, Real tau_r) { return -ssat_r/(ab*tau_r); }
 
@@ -574,7 +574,7 @@ struct Procs {
     const bool do_log = (!do_predict_nc || do_prescribed_CCN);
     const bool any_if_log = cond && !do_log, any_if_not_log = cond && do_log;
     if (any_if_not_log) {
-      Real dum = sp(0.005)*std::exp(sp(ro.deposition_nucleation_exponent)*(tmelt-temp))*sp(1.0e3)*inv_rho;
+      Real dum = sp(0.005)*pm::exp(sp(ro.deposition_nucleation_exponent)*(tmelt-temp))*sp(1.0e3)*inv_rho;
       dum = min(dum, sp(1.0e5)*inv_rho);
       const Real N_nuc = max(zero, (dum-ni)*inv_dt);
       if (N_nuc >= nsmall) {
@@ -594,12 +594,12 @@ struct Procs {
     const bool qc_not_small = qc_incld >= sp(1e-8);
     Real CONS3;
     if (ro.autoconversion_radius == sp(25.0e-6)) CONS3 = C::CONS3;
-    else CONS3 = sp(1.0) / (C::CONS2 * std::pow(ro.autoconversion_radius, sp(3.0)));
+    else CONS3 = sp(1.0) / (C::CONS2 * pm::pow(ro.autoconversion_radius, sp(3.0)));
     if (qc_not_small) {
       const Real sgs_var_coef = 1;
       qc2qr_autoconv_tend = sgs_var_coef * ro.autoconversion_prefactor *
-          std::pow(qc_incld, ro.autoconversion_qc_exponent) *
-          std::pow(nc_incld * sp(1.e-6) * rho, -ro.autoconversion_nc_exponent);
+          pm::pow(qc_incld, ro.autoconversion_qc_exponent) *
+          pm::pow(nc_incld * sp(1.e-6) * rho, -ro.autoconversion_nc_exponent);
       ncautr = qc2qr_autoconv_tend * CONS3;
       nc2nr_autoconv_tend = qc2qr_autoconv_tend * nc_incld / qc_incld;
     }
@@ -620,10 +620,10 @@ struct Procs {
     if ((qr_incld >= qsmall) && (qc_incld >= qsmall)) {
       if (ro.accretion_qc_exponent == ro.accretion_qr_exponent) {
         qc2qr_accret_tend = sgs_var_coef * ro.accretion_prefactor *
-            std::pow(qc_incld * qr_incld, ro.accretion_qr_exponent);
+            pm::pow(qc_incld * qr_incld, ro.accretion_qr_exponent);
       } else {
         qc2qr_accret_tend = sgs_var_coef * ro.accretion_prefactor *
-            std::pow(qc_incld, ro.accretion_qc_exponent) * std::pow(qr_incld, ro.accretion_qr_exponent);
+            pm::pow(qc_incld, ro.accretion_qc_exponent) * pm::pow(qr_incld, ro.accretion_qr_exponent);
       }
       nc_accret_tend = qc2qr_accret_tend * nc_incld / qc_incld;
       if (nc_accret_tend == 0) qc2qr_accret_tend = 0;
@@ -637,10 +637,10 @@ struct Procs {
     const Real qsmall = C::QSMALL, rho_h2o = C::RHO_H2O, pi = C::Pi;
     const Real dbrk = ro.rain_selfcollection_breakup_diameter;
     if (qr_incld >= qsmall) {
-      const Real dum2 = std::cbrt((qr_incld) / (pi * rho_h2o * nr_incld));
+      const Real dum2 = pm::cbrt((qr_incld) / (pi * rho_h2o * nr_incld));
       Real dum;
       if (dum2 < dbrk) dum = 1;
-      else             dum = 2 - std::exp(2300 * (dum2 - dbrk));
+      else             dum = 2 - pm::exp(2300 * (dum2 - dbrk));
       nr_selfcollect_tend = dum * ro.rain_selfcollection_prefactor * nr_incld * qr_incld * rho;
     }
   }

@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <limits>
 #include <algorithm>
+#include "p3_oracle_math.hpp"
 
 namespace p3o {
 

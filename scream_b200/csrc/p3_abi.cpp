@@ -32,10 +32,13 @@ int cuda_fail(cudaError_t e, const char* what) {
     if (e__ != cudaSuccess) return cuda_fail(e__, #call);   \
   } while (0)
 
-constexpr int NQUEUE = 64;        // ring of work-queue counters so launches on different streams never share one
+constexpr int NQUEUE = 64;        // ring of work-queue counter groups so p3_main calls in flight on different streams never share one
+constexpr int QSTRIDE = 16;       // counters per group: one per sedimentation launch (3 species x NUM_SED_CLASSES) + pad
 constexpr int NSLOT = 3;          // host pipeline depth (H2D / kernel / D2H in flight)
 
-struct EventPair { cudaEvent_t a = nullptr, b = nullptr; };
+// events around and between the five launches of one p3_main: m[0] = start, m[EV_END] = end
+struct EventPair { cudaEvent_t m[NUM_PHASE_MARKS] = {nullptr}; };
+constexpr int EV_END = NUM_PHASE_MARKS - 1;
 
 struct Slot {                     // one in-flight column chunk of p3b200_main_host
   cudaStream_t stream = nullptr;
@@ -96,8 +99,7 @@ int upload_tables(p3b200_ctx* h, const P3B200Tables& t) {
 int ensure_events(p3b200_ctx* h, size_t n) {
   while (h->events.size() < n) {
     EventPair p;
-    CU(cudaEventCreate(&p.a));
-    CU(cudaEventCreate(&p.b));
+    for (int i = 0; i < NUM_PHASE_MARKS; ++i) CU(cudaEventCreate(&p.m[i]));
     h->events.push_back(p);
   }
   return P3B200_OK;
@@ -133,18 +135,16 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
   if (runtime) r = *runtime; else runtime_defaults(r);
   a.ro = make_runtime<Real>(r);
   a.diag = diag;
-  a.queue = h->d_queue + h->next_queue;
+  a.queue = h->d_queue + h->next_queue * QSTRIDE;
   h->next_queue = (h->next_queue + 1) % NQUEUE;
   if (h->cfg_nk != in->nlev || h->cfg_ncol != ncol) {
     const int rc = plan_launch<Real>(in->nlev, ncol, &h->cfg);
     if (rc) return cuda_fail((cudaError_t)rc, "plan_launch");
     h->cfg_nk = in->nlev; h->cfg_ncol = ncol;
   }
-  CU(cudaMemsetAsync(a.queue, 0, sizeof(unsigned int), stream));
-  if (ev) CU(cudaEventRecord(ev->a, stream));
-  const int rc = launch_main<Real>(a, h->cfg, stream);
+  CU(cudaMemsetAsync(a.queue, 0, QSTRIDE * sizeof(unsigned int), stream));
+  const int rc = launch_main<Real>(a, h->cfg, stream, ev ? reinterpret_cast<void* const*>(ev->m) : nullptr);
   if (rc) return cuda_fail((cudaError_t)rc, "p3_main_kernel launch");
-  if (ev) CU(cudaEventRecord(ev->b, stream));
   return P3B200_OK;
 }
 
@@ -211,7 +211,7 @@ int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p
   h->real_bytes = real_bytes;
   int rc = real_bytes == 8 ? upload_tables<double>(h, *host_tables) : upload_tables<float>(h, *host_tables);
   if (rc == P3B200_OK) {
-    e = cudaMalloc(&h->d_queue, NQUEUE * sizeof(unsigned int));
+    e = cudaMalloc(&h->d_queue, NQUEUE * QSTRIDE * sizeof(unsigned int));
     if (e != cudaSuccess) rc = cuda_fail(e, "cudaMalloc queue");
   }
   if (rc != P3B200_OK) { p3b200_destroy(h); return rc; }
@@ -223,7 +223,7 @@ int p3b200_destroy(p3b200_handle h) {
   if (!h) return P3B200_EINVAL;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
-  for (auto& p : h->events) { if (p.a) cudaEventDestroy(p.a); if (p.b) cudaEventDestroy(p.b); }
+  for (auto& p : h->events) for (int i = 0; i < NUM_PHASE_MARKS; ++i) if (p.m[i]) cudaEventDestroy(p.m[i]);
   for (auto& s : h->slots) {
     if (s.dev) cudaFree(s.dev);
     if (s.diag) cudaFree(s.diag);
@@ -263,9 +263,9 @@ int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Field
   if (rc) return rc;
   h->events_used = 1;
   if (elapsed_us) {
-    CU(cudaEventSynchronize(h->events[0].b));
+    CU(cudaEventSynchronize(h->events[0].m[EV_END]));
     float ms = 0;
-    CU(cudaEventElapsedTime(&ms, h->events[0].a, h->events[0].b));
+    CU(cudaEventElapsedTime(&ms, h->events[0].m[0], h->events[0].m[EV_END]));
     *elapsed_us = (int64_t)(ms * 1000.0f + 0.5f);
   }
   return P3B200_OK;
@@ -298,13 +298,28 @@ int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches) {
   CU(cudaSetDevice(h->device));
   double total = 0;
   for (size_t i = 0; i < h->events_used; ++i) {
-    CU(cudaEventSynchronize(h->events[i].b));
+    CU(cudaEventSynchronize(h->events[i].m[EV_END]));
     float t = 0;
-    CU(cudaEventElapsedTime(&t, h->events[i].a, h->events[i].b));
+    CU(cudaEventElapsedTime(&t, h->events[i].m[0], h->events[i].m[EV_END]));
     total += t;
   }
   *ms = total;
   if (launches) *launches = (int64_t)h->events_used;
+  return P3B200_OK;
+}
+
+int p3b200_last_phase_ms(p3b200_handle h, double* ms5) {
+  if (!h || !ms5) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  for (int p = 0; p < EV_END; ++p) ms5[p] = 0;
+  for (size_t i = 0; i < h->events_used; ++i) {
+    CU(cudaEventSynchronize(h->events[i].m[EV_END]));
+    for (int p = 0; p < EV_END; ++p) {
+      float t = 0;
+      CU(cudaEventElapsedTime(&t, h->events[i].m[p], h->events[i].m[p + 1]));
+      ms5[p] += t;
+    }
+  }
   return P3B200_OK;
 }
 

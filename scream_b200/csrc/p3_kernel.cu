@@ -1,14 +1,23 @@
-// p3_kernel.cu — the sm_100a kernel of libp3b200: p3_main for a batch of columns.
+// p3_kernel.cu — the sm_100a kernels of libp3b200: p3_main for a batch of columns.
 //
-// Execution model (replaces the Kokkos TeamPolicy of p3_main_impl.hpp:86-113, one team per column):
-//   - one WARP owns one column at a time; the 32 lanes stride over the levels (lane l owns levels
-//     l, l+32, ...), so every global access of a warp is one contiguous 256-byte (fp64) row segment;
-//   - warps are persistent and independent: each pulls the next column index from a global atomic
-//     counter, which absorbs the load imbalance of the CFL sub-stepping (columns with rain need tens
-//     of sub-steps, clear-sky columns none) without sorting;
-//   - the column working set (16 rows of nk Reals, ColumnSmem) lives in the warp's private slice of
-//     dynamic shared memory; cross-lane traffic is warp shuffles + __syncwarp only, no __syncthreads;
-//   - the lookup tables (0.65 MB fp64) are read through the read-only path and stay L2/L1 resident.
+// Execution model (replaces the Kokkos TeamPolicy of p3_main_impl.hpp:86-113, one team per column,
+// all phases in one kernel separated by team barriers).  p3_main is a short sequence of launches on one stream:
+//
+//   p3_phase_a   init + part1 + part2.  One WARP per column, the 32 lanes stride over the levels, so
+//                every global access of a warp is one contiguous 256-byte (fp64) row segment.  Level
+//                parallel, register heavy (255 regs), no serial dependency between levels.
+//   p3_sediment<cloud|rain|ice, JW>
+//                CFL sub-stepped sedimentation, one launch per species and window class (JW = 1,2,4,8
+//                register slots per lane).  One warp per column that holds the species, window of
+//                reachable levels in registers, warp shuffles for the upwind flux, redux for the Courant
+//                maximum.  Persistent warps pull chunks of columns from an atomic counter, which absorbs
+//                the load imbalance (columns with rain need tens of sub-steps, most need none).  Few
+//                registers per thread -> 3-8x the resident warps of phase A to hide the latency of the
+//                serial sub-step chain.
+//   p3_phase_c   homogeneous freezing + part3.  One THREAD per (column, level).
+//
+// No __syncthreads anywhere: cross-lane traffic is shuffles/redux inside a warp.  The lookup tables
+// (0.65 MB fp64) are read through the read-only path and stay L2/L1 resident.
 #include "p3_kernel.cuh"
 
 #include <cuda_runtime.h>
@@ -20,15 +29,18 @@ struct WarpDev {
   static constexpr unsigned FULL = 0xffffffffu;
   __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
   __device__ __forceinline__ bool any(bool b) const { return __any_sync(FULL, b) != 0; }
-  __device__ __forceinline__ double max_real(double v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { const double u = __shfl_xor_sync(FULL, v, o); v = (v < u) ? u : v; }
-    return v;
+  // warp maximum of NON-NEGATIVE values: IEEE bit patterns of non-negative numbers order like unsigned
+  // integers, so two redux.sync (high word, then low word among the lanes holding the max high word)
+  // replace the 5-round shuffle tree.  A NaN or a negative input yields a NaN/negative result, which the
+  // caller flags (Co_max >= 0 is asserted by the reference too, p3_upwind_impl.hpp:108).
+  __device__ __forceinline__ double max_nonneg(double v) const {
+    const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+    const unsigned mhi = __reduce_max_sync(FULL, hi);
+    const unsigned mlo = __reduce_max_sync(FULL, hi == mhi ? lo : 0u);
+    return __hiloint2double((int)mhi, (int)mlo);
   }
-  __device__ __forceinline__ float max_real(float v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { const float u = __shfl_xor_sync(FULL, v, o); v = (v < u) ? u : v; }
-    return v;
+  __device__ __forceinline__ float max_nonneg(float v) const {
+    return __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(v)));
   }
   __device__ __forceinline__ int min_int(int v) const { return __reduce_min_sync(FULL, v); }
   __device__ __forceinline__ int max_int(int v) const { return __reduce_max_sync(FULL, v); }
@@ -39,73 +51,158 @@ struct WarpDev {
   template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
 };
 
-template <typename Real, int JM>
-__global__ void __launch_bounds__(128)
-p3_main_kernel(const __grid_constant__ MainArgs<Real> a) {
+constexpr int A_WARPS = 4;        // warps (columns) per CTA in phase A
+constexpr int B_WARPS = 4;        // warps per CTA in the sedimentation kernels
+constexpr int C_THREADS = 256;
+
+template <typename Real>
+__global__ void __launch_bounds__(A_WARPS * 32)
+p3_phase_a(const __grid_constant__ MainArgs<Real> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
-  Real* smem = reinterpret_cast<Real*>(smem_raw) + size_t(warp) * NUM_SMEM_ROWS * a.nk;
+  Real* hist = reinterpret_cast<Real*>(smem_raw) + size_t(warp) * HIST_ROWS * a.nk;
+  const int64_t col = (int64_t)blockIdx.x * A_WARPS + warp;
+  if (col >= a.ncol) return;
+  WarpDev w;
+  PhaseA<Real, WarpDev>::run(w, a, col, hist);
+}
+
+// Sedimentation of species SP for the columns whose window [k_qxtop, nk) needs exactly JW register slots
+// per lane (JW in {1,2,4,8} covers up to 32*JW levels).  One launch per (species, JW): each instantiation
+// gets the register budget its window needs, so the common short windows (rain and cloud live in the
+// lowest 20-30 levels) run at 2-4x the occupancy of the tall ones.  Persistent warps grab chunks of
+// `chunk` (<= 32) consecutive columns from the launch's own atomic counter; lane i of the warp looks up
+// the range of column i of the chunk, a ballot selects the columns of this launch's class.
+constexpr int sed_min_blocks(int JW) { return JW == 1 ? 8 : JW == 2 ? 5 : JW == 4 ? 3 : 2; }
+__host__ __device__ constexpr int sed_class(int need) { return need <= 1 ? 1 : need <= 2 ? 2 : need <= 4 ? 4 : 8; }
+
+template <typename Real, int SP, int JW>
+__global__ void __launch_bounds__(B_WARPS * 32, sed_min_blocks(JW))
+p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__ counter, const int chunk) {
   WarpDev w;
   const int lane = w.lane();
+  constexpr int dbase = (SP == SP_CLOUD) ? D_QC_KTOP : (SP == SP_RAIN) ? D_QR_KTOP : D_QI_KTOP;
+  const unsigned nchunks = ((unsigned)a.ncol + chunk - 1) / chunk;
   for (;;) {
-    unsigned int col = 0;
-    if (lane == 0) col = atomicAdd(a.queue, 1u);
-    col = __shfl_sync(WarpDev::FULL, col, 0);
-    if (col >= (unsigned)a.ncol) break;
-    Column<Real, WarpDev, JM>::run(w, a, (int64_t)col, smem);
+    unsigned c = 0;
+    if (lane == 0) c = atomicAdd(counter, 1u);
+    c = __shfl_sync(WarpDev::FULL, c, 0);
+    if (c >= nchunks) break;
+    const int64_t c0 = (int64_t)c * chunk;
+    int ktop = -1, kbot = -1;
+    if (lane < chunk && c0 + lane < a.ncol) {
+      const int* d = a.diag + (c0 + lane) * D_NUM + dbase;
+      ktop = d[0]; kbot = d[1];
+    }
+    const bool mine = ktop >= 0 && sed_class((a.nk - 1 - ktop) / 32 + 1) == JW;
+    unsigned todo = __ballot_sync(WarpDev::FULL, mine);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int kt = __shfl_sync(WarpDev::FULL, ktop, src);
+      const int kb = __shfl_sync(WarpDev::FULL, kbot, src);
+      Sediment<Real, WarpDev, SP, JW>::run(w, a, c0 + src, kt, kb);
+    }
   }
 }
 
-template <typename Real, int JM>
-static int plan_for(int nk, int ncol, int sms, int max_optin, LaunchConfig* cfg) {
-  const int per_warp = NUM_SMEM_ROWS * nk * (int)sizeof(Real);
-  int wpb = 4;
-  while (wpb > 1 && wpb * per_warp > max_optin) wpb >>= 1;
-  if (wpb * per_warp > max_optin) return (int)cudaErrorInvalidValue;
-  cfg->warps_per_block = wpb;
-  cfg->smem_bytes = wpb * per_warp;
-  cudaError_t e = cudaFuncSetAttribute(p3_main_kernel<Real, JM>, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg->smem_bytes);
-  if (e != cudaSuccess) return (int)e;
+template <typename Real>
+__global__ void __launch_bounds__(C_THREADS, 4)
+p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
+  const int64_t idx = (int64_t)blockIdx.x * C_THREADS + threadIdx.x;
+  int64_t col;
+  if (idx < (int64_t(1) << 32)) col = (int64_t)((unsigned)idx / (unsigned)a.nk);   // 32-bit divide on the common sizes
+  else col = idx / a.nk;
+  if (col >= a.ncol) return;
+  const int k = (int)(idx - col * a.nk);
+  if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) return;   // the column left p3_main before sedimentation
+  PhaseC<Real>::level(a, col, k);
+}
+
+template <typename Kernel>
+static int occupancy_blocks(Kernel k, int threads, int smem, int sms, long long need, int* out) {
   int bps = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, p3_main_kernel<Real, JM>, wpb * 32, cfg->smem_bytes);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k, threads, smem);
   if (e != cudaSuccess) return (int)e;
   if (bps < 1) return (int)cudaErrorLaunchOutOfResources;
-  cfg->blocks_per_sm = bps;
   long long blocks = (long long)sms * bps;
-  const long long need = ((long long)ncol + wpb - 1) / wpb;
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  cfg->blocks = (int)blocks;
+  *out = (int)blocks;
   return 0;
 }
 
-// Two instantiations per precision: JM = 4 register slots per lane (nk <= 128, the production grids)
-// and JM = 8 (nk <= 256).
+template <typename Real, int SP>
+static int plan_species(int sms, long long need, int nk, int* out /* [NUM_SED_CLASSES] */) {
+  int rc;
+  if ((rc = occupancy_blocks(p3_sediment<Real, SP, 1>, B_WARPS * 32, 0, sms, need, out + 0))) return rc;
+  if ((rc = occupancy_blocks(p3_sediment<Real, SP, 2>, B_WARPS * 32, 0, sms, need, out + 1))) return rc;
+  if ((rc = occupancy_blocks(p3_sediment<Real, SP, 4>, B_WARPS * 32, 0, sms, need, out + 2))) return rc;
+  out[3] = 0;
+  if (nk > 128 && (rc = occupancy_blocks(p3_sediment<Real, SP, 8>, B_WARPS * 32, 0, sms, need, out + 3))) return rc;
+  if (nk <= 64) out[2] = 0;     // windows never need more than 2 slots
+  if (nk <= 32) out[1] = 0;
+  return 0;
+}
+
 template <typename Real>
 int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
-  int dev = 0, sms = 0, max_optin = 0;
+  int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return (int)e;
-  e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  if (e != cudaSuccess) return (int)e;
-  if (nk > MAX_NLEV) return (int)cudaErrorInvalidValue;
-  return nk <= 128 ? plan_for<Real, 4>(nk, ncol, sms, max_optin, cfg) : plan_for<Real, 8>(nk, ncol, sms, max_optin, cfg);
+  if (nk < 1 || nk > MAX_NLEV) return (int)cudaErrorInvalidValue;
+  cfg->a_blocks = (ncol + A_WARPS - 1) / A_WARPS;
+  cfg->a_smem = A_WARPS * HIST_ROWS * nk * (int)sizeof(Real);
+  // chunk of the sedimentation work queues: as large as 32 columns (one per lane) when there is plenty of
+  // work, smaller when the grid is small so that the slowest warp does not hold the tail
+  int chunk = 32;
+  while (chunk > 1 && (long long)ncol < (long long)sms * 64 * chunk) chunk >>= 1;
+  cfg->b_chunk = chunk;
+  const long long need = ((long long)ncol + (long long)B_WARPS * chunk - 1) / ((long long)B_WARPS * chunk);
+  int rc;
+  if ((rc = plan_species<Real, SP_CLOUD>(sms, need, nk, cfg->b_blocks[0]))) return rc;
+  if ((rc = plan_species<Real, SP_RAIN>(sms, need, nk, cfg->b_blocks[1]))) return rc;
+  if ((rc = plan_species<Real, SP_ICE>(sms, need, nk, cfg->b_blocks[2]))) return rc;
+  const long long levels = (long long)ncol * nk;
+  cfg->c_blocks = (int)((levels + C_THREADS - 1) / C_THREADS);
+  return 0;
+}
+
+template <typename Real, int SP>
+static void launch_species(const MainArgs<Real>& a, const LaunchConfig& cfg, cudaStream_t stream) {
+  const int* nb = cfg.b_blocks[SP];
+  unsigned int* q = a.queue + SP * NUM_SED_CLASSES;
+  if (nb[0]) p3_sediment<Real, SP, 1><<<nb[0], B_WARPS * 32, 0, stream>>>(a, q + 0, cfg.b_chunk);
+  if (nb[1]) p3_sediment<Real, SP, 2><<<nb[1], B_WARPS * 32, 0, stream>>>(a, q + 1, cfg.b_chunk);
+  if (nb[2]) p3_sediment<Real, SP, 4><<<nb[2], B_WARPS * 32, 0, stream>>>(a, q + 2, cfg.b_chunk);
+  if (nb[3]) p3_sediment<Real, SP, 8><<<nb[3], B_WARPS * 32, 0, stream>>>(a, q + 3, cfg.b_chunk);
 }
 
 template <typename Real>
-int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream) {
-  if (a.nk <= 128)
-    p3_main_kernel<Real, 4><<<cfg.blocks, cfg.warps_per_block * 32, cfg.smem_bytes, (cudaStream_t)stream>>>(a);
-  else
-    p3_main_kernel<Real, 8><<<cfg.blocks, cfg.warps_per_block * 32, cfg.smem_bytes, (cudaStream_t)stream>>>(a);
+int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (a.ncol <= 0) return 0;
+  auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
+  mark(0);
+  p3_phase_a<Real><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+  mark(1);
+  // stream order cloud -> rain -> ice: precip_liq_surf is assigned by cloud and incremented by rain
+  launch_species<Real, SP_CLOUD>(a, cfg, stream);
+  mark(2);
+  launch_species<Real, SP_RAIN>(a, cfg, stream);
+  mark(3);
+  launch_species<Real, SP_ICE>(a, cfg, stream);
+  mark(4);
+  p3_phase_c<Real><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  mark(5);
   return (int)cudaGetLastError();
 }
 
 template int plan_launch<double>(int, int, LaunchConfig*);
 template int plan_launch<float>(int, int, LaunchConfig*);
-template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*);
-template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*);
+template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*);
+template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*);
 
 }  // namespace p3b200

@@ -7,21 +7,25 @@
 
 namespace p3b200 {
 
+constexpr int NUM_SED_CLASSES = 4;   // register-window classes of the sedimentation launches: 1, 2, 4, 8 slots per lane
+
 struct LaunchConfig {
-  int warps_per_block;   // independent warps per CTA (no block-level sync is ever used)
-  int blocks;            // persistent grid: SM count x resident CTAs per SM
-  int smem_bytes;        // dynamic shared memory per CTA
-  int blocks_per_sm;     // occupancy the config was sized for
+  int a_blocks, a_smem;     // phase A: one warp per column, dynamic shared memory for the history rows
+  int b_blocks[3][NUM_SED_CLASSES];   // sedimentation [cloud, rain, ice][JW = 1,2,4,8]: persistent grids (0 = class unused)
+  int b_chunk;              // columns per work-queue grab (<= 32)
+  int c_blocks;             // phase C: one thread per (column, level)
 };
 
-// Size a persistent grid for `nk` levels on the current device.  Returns a cudaError_t as int.
+// Size the five launches for `ncol` columns of `nk` levels on the current device.  Returns a cudaError_t as int.
 template <typename Real>
 int plan_launch(int nk, int ncol, LaunchConfig* cfg);
 
-// Enqueue p3_main for all columns of `a` on `stream` (a cudaStream_t).  `a.queue` must point to a
-// zeroed device counter.  Returns a cudaError_t as int.
+// Enqueue p3_main for all columns of `a` on `stream` (a cudaStream_t).  `a.queue` must point to
+// 3*NUM_SED_CLASSES zeroed device counters.  Returns a cudaError_t as int.
+// `marks`: optional 6 cudaEvent_t recorded before phase A, after phase A, after each species' sedimentation launches and after phase C (NUM_PHASE_MARKS).
+constexpr int NUM_PHASE_MARKS = 6;
 template <typename Real>
-int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream);
+int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks);
 
 }  // namespace p3b200
 #endif

@@ -22,7 +22,8 @@ ABI_SYMBOLS = [
     "p3b200_abi_version", "p3b200_strerror", "p3b200_last_cuda_error", "p3b200_device_count",
     "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
-    "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_set_default_tables",
+    "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
+    "p3b200_set_default_tables",
     "p3b200_p3_main_f",
 ]
 
@@ -90,6 +91,7 @@ def lib():
         L.p3b200_error_summary.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
         L.p3b200_last_kernel_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
                                             ctypes.POINTER(ctypes.c_int64)]
+        L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
         L.p3b200_tables_read_text.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
         L.p3b200_tables_read_blob.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
@@ -237,6 +239,12 @@ class P3Handle:
         n = ctypes.c_int64(0)
         check(lib().p3b200_last_kernel_ms(self._h, ctypes.byref(ms), ctypes.byref(n)), "p3b200_last_kernel_ms")
         return ms.value, n.value
+
+    def last_phase_ms(self):
+        """Device ms of the five launches of the last call: phase A, cloud/rain/ice sedimentation, phase C."""
+        ms = (ctypes.c_double * 5)()
+        check(lib().p3b200_last_phase_ms(self._h, ms), "p3b200_last_phase_ms")
+        return dict(zip(("phase_a", "sed_cloud", "sed_rain", "sed_ice", "phase_c"), [float(x) for x in ms]))
 
 
 def to_device(fields, device="cuda:0"):

@@ -13,7 +13,7 @@ struct WarpSim {
   static constexpr int size = 1;
   int lane() const { return 0; }
   bool any(bool b) const { return b; }
-  template <class R> R max_real(R v) const { return v; }
+  template <class R> R max_nonneg(R v) const { return v; }
   int min_int(int v) const { return v; }
   int max_int(int v) const { return v; }
   int or_int(int v) const { return v; }
@@ -41,10 +41,28 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   P3B200Runtime r;
   if (rt) r = *rt; else runtime_defaults(r);
   a.ro = make_runtime<Real>(r);
+  std::vector<int> own_diag;
+  if (!diag) { own_diag.assign(size_t(ncol) * D_NUM, 0); diag = own_diag.data(); }
   a.diag = diag; a.queue = nullptr;
-  std::vector<Real> smem(size_t(NUM_SMEM_ROWS) * nlev);
+  std::vector<Real> hist(size_t(HIST_ROWS) * nlev);
   WarpSim w;
-  for (int i = 0; i < ncol; ++i) Column<Real, WarpSim, p3b200::MAX_NLEV>::run(w, a, i, smem.data());
+  // the three phases in the order the kernels run them (p3_kernel.cu: launch_main)
+  for (int i = 0; i < ncol; ++i) PhaseA<Real, WarpSim>::run(w, a, i, hist.data());
+  for (int i = 0; i < ncol; ++i) {
+    const int* d = diag + size_t(i) * D_NUM;
+    if (d[D_QC_KTOP] >= 0) Sediment<Real, WarpSim, SP_CLOUD, p3b200::MAX_NLEV>::run(w, a, i, d[D_QC_KTOP], d[D_QC_KBOT]);
+  }
+  for (int i = 0; i < ncol; ++i) {
+    const int* d = diag + size_t(i) * D_NUM;
+    if (d[D_QR_KTOP] >= 0) Sediment<Real, WarpSim, SP_RAIN, p3b200::MAX_NLEV>::run(w, a, i, d[D_QR_KTOP], d[D_QR_KBOT]);
+  }
+  for (int i = 0; i < ncol; ++i) {
+    const int* d = diag + size_t(i) * D_NUM;
+    if (d[D_QI_KTOP] >= 0) Sediment<Real, WarpSim, SP_ICE, p3b200::MAX_NLEV>::run(w, a, i, d[D_QI_KTOP], d[D_QI_KBOT]);
+  }
+  for (int i = 0; i < ncol; ++i)
+    if (diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1)
+      for (int k = 0; k < nlev; ++k) PhaseC<Real>::level(a, i, k);
   return 0;
 }
 }  // namespace

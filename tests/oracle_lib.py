@@ -47,6 +47,8 @@ def lib():
                                ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_int,
                                ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
         L.p3o_max_threads.restype = ctypes.c_int
+        L.p3o_set_math_scale.restype = None
+        L.p3o_set_math_scale.argtypes = [ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -121,6 +123,20 @@ def p3_main(fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None, nthr
     if t < 0:
         raise RuntimeError(f"p3o_main failed rc={t}")
     return t, diag
+
+
+MATH_FUNCS = ("pow", "exp", "log", "log10", "cbrt", "tgamma", "tanh", "expm1")
+
+
+def set_math_scale(scale=None):
+    """Conditioning probe (oracle/p3_oracle_math.hpp): multiply the result of every transcendental call by
+    scale[fn] (8 values in MATH_FUNCS order, or one value for all); None restores exact libm."""
+    if scale is None:
+        lib().p3o_set_math_scale(None)
+        return
+    arr = np.full(len(MATH_FUNCS), scale, dtype=np.float64) if np.isscalar(scale) else np.asarray(scale, dtype=np.float64)
+    assert arr.shape == (len(MATH_FUNCS),)
+    lib().p3o_set_math_scale(arr.ctypes.data)
 
 
 def max_threads():

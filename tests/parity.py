@@ -56,6 +56,45 @@ def column_mismatch(ref, got, tol, names=OUTPUTS):
     return bad
 
 
+ULP = {8: 2.0 ** -52, 4: 2.0 ** -23}
+
+
+def stable_columns(oracle, fields, dt, predict_nc, prescribed_ccn, ref=None, d_ref=None, tol=None):
+    """Conditioning probe.  P3 is a cascade of thresholds (qsmall gates, int(Co_max+1) sub-step counts,
+    table-cell truncation) and the reference concedes that std:: and CUDA math differ in the last bit
+    (physics_share.cpp:17): for some columns that last bit decides the outcome.  This re-runs the ORACLE
+    with the result of every transcendental call scaled by (1 +- 1 ulp), one function family at a time and
+    all together, and returns the boolean mask of columns whose outputs stay within `tol` (default: a tenth
+    of the parity tolerance) and whose integer diagnostics do not move.  Only those columns can be expected
+    to agree between ANY two correct implementations that use different math libraries."""
+    rb = fields["qc"].dtype.itemsize
+    tol = TOL[rb] / 10 if tol is None else tol
+    if ref is None:
+        ref = clone(fields)
+        zero_outputs(ref)
+        _, d_ref = oracle.p3_main(ref, dt, predict_nc, prescribed_ccn)
+    ncol = fields["qc"].shape[0]
+    stable = np.ones(ncol, dtype=bool)
+    n = len(oracle.MATH_FUNCS)
+    probes = [np.full(n, 1 + ULP[rb]), np.full(n, 1 - ULP[rb])]
+    for i in range(n):
+        for sgn in (+1, -1):
+            p = np.ones(n)
+            p[i] = 1 + sgn * ULP[rb]
+            probes.append(p)
+    try:
+        for p in probes:
+            oracle.set_math_scale(p)
+            alt = clone(fields)
+            zero_outputs(alt)
+            _, d_alt = oracle.p3_main(alt, dt, predict_nc, prescribed_ccn)
+            stable &= ~column_mismatch(ref, alt, tol)
+            stable &= ~(d_ref != d_alt).any(axis=1)
+    finally:
+        oracle.set_math_scale(None)
+    return stable
+
+
 def run_pair(oracle, handle, fields, dt, predict_nc, prescribed_ccn, nsteps=1, host_path=False):
     """Step oracle and GPU side by side from the same start; returns (ref, got, diag_ref, diag_got)."""
     from scream_b200 import lib as p3

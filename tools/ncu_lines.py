@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Attribute an `ncu --page source --csv` SASS profile to source lines of the product code.
 
-usage: tools/ncu_lines.py <report.ncu-rep> <cubin> <kernel-mangled-substring> [--top N]
+usage: tools/ncu_lines.py <report.ncu-rep> <cubin> <kernel-mangled-substring> [--top N] [--launch <demangled-substring>]
 
 Joins ncu's per-SASS-instruction counters (instructions executed, stall samples) with the line info
 `nvdisasm -c -gi` prints for the same cubin (built with -lineinfo), by instruction offset.  Every
@@ -52,8 +52,17 @@ def main():
     top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 40
     raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     lines = raw.splitlines()
+    # one section per profiled launch: "Kernel Name",<demangled> then the "Address",... table
+    want = sys.argv[sys.argv.index("--launch") + 1] if "--launch" in sys.argv else None
+    heads = [i for i, l in enumerate(lines) if l.startswith('"Kernel Name"')]
+    if heads and want is not None:
+        h = next(i for i in heads if want in lines[i])
+        end = next((j for j in heads if j > h), len(lines))
+        lines = lines[h:end]
+        print("launch:", lines[0][:120])
     start = next(i for i, l in enumerate(lines) if l.startswith('"Address"'))
-    rows = list(csv.DictReader(io.StringIO("\n".join(lines[start:]))))
+    end = next((j for j in range(start + 1, len(lines)) if lines[j].startswith('"Kernel Name"')), len(lines))
+    rows = list(csv.DictReader(io.StringIO("\n".join(lines[start:end]))))
     base = int(rows[0]["Address"], 16)
     dis = disasm(cubin, kernel)
     by_phase = collections.Counter()
