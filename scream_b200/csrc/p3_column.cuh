@@ -335,7 +335,7 @@ struct Sediment {
         if (SP == SP_RAIN) acc[j] = g_plf[k + 1];
         if (SP == SP_CLOUD) {   // acn = g*rhow/(18*mu_air(T_atm at init)), p3_main_impl_part1.hpp:108-109
           const Real T0 = std::abs(g_stash[k]);
-          const Real dum = sp(1.496e-6) * std::pow(T0, sp(1.5)) / (T0 + 120);
+          const Real dum = sp(1.496e-6) * P::pow1p5(T0) / (T0 + 120);
           fac[j] = C::gravit * C::RHO_H2O / (18 * dum);
         } else if (SP == SP_RAIN) {
           fac[j] = std::pow(C::RHO_1000MB * inv_rho[j], sp(.54));   // rhofacr, p3_main_impl_part1.hpp:105

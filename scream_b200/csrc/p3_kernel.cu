@@ -21,6 +21,7 @@
 #include "p3_kernel.cuh"
 
 #include <cuda_runtime.h>
+#include <cstdlib>
 
 namespace p3b200 {
 
@@ -55,8 +56,8 @@ constexpr int A_WARPS = 4;        // warps (columns) per CTA in phase A
 constexpr int B_WARPS = 4;        // warps per CTA in the sedimentation kernels
 constexpr int C_THREADS = 256;
 
-template <typename Real>
-__global__ void __launch_bounds__(A_WARPS * 32)
+template <typename Real, int MINB>
+__global__ void __launch_bounds__(A_WARPS * 32, MINB)
 p3_phase_a(const __grid_constant__ MainArgs<Real> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
@@ -186,7 +187,12 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   if (a.ncol <= 0) return 0;
   auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
   mark(0);
-  p3_phase_a<Real><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+  {
+    static const int occ = [] { const char* e = getenv("P3B200_A_OCC"); return e ? atoi(e) : 4; }();
+    if (occ == 3) p3_phase_a<Real, 3><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+    else if (occ == 4) p3_phase_a<Real, 4><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+    else p3_phase_a<Real, 2><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+  }
   mark(1);
   // stream order cloud -> rain -> ice: precip_liq_surf is assigned by cloud and incremented by rain
   launch_species<Real, SP_CLOUD>(a, cfg, stream);

@@ -19,31 +19,36 @@ SRC = [os.path.join(ROOT, "tests", "hostsim", "p3_hostsim.cpp"),
        os.path.join(ROOT, "scream_b200", "csrc", "p3_host.cpp")]
 DEPS = SRC + [os.path.join(ROOT, "scream_b200", "csrc", f) for f in
               ("p3_column.cuh", "p3_physics.cuh", "p3_host.hpp")] + [os.path.join(ROOT, "include", "p3_b200.h")]
-LIB_PATH = os.path.join(ROOT, "build", "libp3hostsim.so")
+# two flavours: "exact" (-DP3B200_EXACT_MATH: the reference's own pow calls, comparable with the oracle to
+# the last bit -> proves the driver logic) and "product" (the arithmetic the GPU build uses, which replaces a
+# few pow calls by 1-ulp-equivalent cheaper forms -> compared on the well-conditioned columns)
+LIB_PATHS = {"exact": os.path.join(ROOT, "build", "libp3hostsim_exact.so"),
+             "product": os.path.join(ROOT, "build", "libp3hostsim.so")}
 
-_lib = None
+_libs = {}
 _tables = None
 
 
-def build():
-    stale = (not os.path.exists(LIB_PATH)) or any(os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in DEPS)
+def build(flavour="exact"):
+    path = LIB_PATHS[flavour]
+    stale = (not os.path.exists(path)) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in DEPS)
     if stale:
-        os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        extra = ["-DP3B200_EXACT_MATH"] if flavour == "exact" else []
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared",
-                               "-I/usr/local/cuda/include", "-o", LIB_PATH] + SRC)
+                               "-I/usr/local/cuda/include"] + extra + ["-o", path] + SRC)
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        build()
-        L = ctypes.CDLL(LIB_PATH)
+def lib(flavour="exact"):
+    if flavour not in _libs:
+        build(flavour)
+        L = ctypes.CDLL(LIB_PATHS[flavour])
         L.p3sim_tables.argtypes = [ctypes.c_char_p, ctypes.POINTER(p3.P3B200Tables)]
         L.p3sim_main.argtypes = [ctypes.POINTER(p3.P3B200Tables), ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                  ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_int,
                                  ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
-        _lib = L
-    return _lib
+        _libs[flavour] = L
+    return _libs[flavour]
 
 
 def tables():
@@ -56,7 +61,7 @@ def tables():
     return _tables
 
 
-def p3_main(fields, dt, predict_nc=True, prescribed_ccn=True, zero_flux_top=True):
+def p3_main(fields, dt, predict_nc=True, prescribed_ccn=True, zero_flux_top=True, flavour="exact"):
     """Run the 1-lane host build in place on a dict of numpy arrays; returns diag[ncol, NUM_DIAG]."""
     qc = fields["qc"]
     ncol, nlev = qc.shape
@@ -69,7 +74,7 @@ def p3_main(fields, dt, predict_nc=True, prescribed_ccn=True, zero_flux_top=True
         ptrs[i] = a.ctypes.data
         strides[i] = (a.strides[0] // rb) if a.ndim == 2 else 1
     diag = np.full((ncol, NUM_DIAG), -7, dtype=np.int32)
-    rc = lib().p3sim_main(ctypes.byref(tables()), rb, ptrs, strides, ncol, nlev, float(dt), int(predict_nc),
+    rc = lib(flavour).p3sim_main(ctypes.byref(tables()), rb, ptrs, strides, ncol, nlev, float(dt), int(predict_nc),
                           int(prescribed_ccn), int(zero_flux_top), None, diag.ctypes.data)
     assert rc == 0, rc
     return diag
