@@ -261,6 +261,18 @@ def run_b200(args):
     total_ms_max = float(tmax.item())
     value = ncol_g * nlev * args.steps / (total_ms_max * 1e-3)
 
+    # ---- the one collective of the path, off the timed region: global water/energy budget of one step
+    from scream_b200 import conservation
+    restore()
+    fields["precip_liq_surf"].zero_(); fields["precip_ice_surf"].zero_()
+    b4 = handle.water_energy_totals(fields, dt, stream)
+    handle.main_prepared(fstruct, infra, stream)
+    a4 = handle.water_energy_totals(fields, dt, stream)
+    b4, a4 = conservation.allreduce_totals(b4, a4, device=dev)      # NCCL all-reduce of 8 doubles when world > 1
+    res_w, res_e = conservation.budget_residuals(b4, a4)
+    budget = {"water_rel_residual": res_w, "energy_rel_residual": res_e, "global_water_kg_m2_sum": float(b4[0]),
+              "collective": "all_reduce(8 x f64, NCCL)" if world > 1 else "none (1 rank)"}
+
     # ---- roofline for the one kernel (p3_main_kernel): algorithmic bytes / event time --------------
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -329,7 +341,7 @@ def run_b200(args):
                            "dt": dt, "columns_per_gpu": ncol, "flags": "predictNc=1,prescribedCCN=1",
                            "parallelism": f"columns block-sharded over {world} GPU(s), no collective in the step",
                            "l2": "inputs 72 GB >> 126 MB L2 and restored (16 GB written) between timed steps"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "roofline": roofline, "conservation": budget, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": 5 * args.steps, "column_error_bits": err_bits,
                 "step_ms": [round(x, 4) for x in step_ms],
                 "phase_ms_last_step": {k: round(v, 4) for k, v in phases.items()}}

@@ -185,6 +185,20 @@ int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches);
  * ms5[4] phase C (homogeneous freezing + part3); each summed over the chunks of the last call. */
 int p3b200_last_phase_ms(p3b200_handle h, double* ms5);
 
+/* ---- global water / energy budget (the one collective of the path: the caller all-reduces 4 doubles) ------
+ * Domain totals over the columns of `fields` (device arrays), formed in double in a fixed order:
+ *   totals4[0] = sum (qv+qc+qi+qr) * dpres / g            water mass            [kg m-2, summed over columns]
+ *   totals4[1] = sum (T*Cpair + (LatVap+LatIce)*qv + LatIce*(qc+qr)) * dpres / g,  T = th/inv_exner   [J m-2]
+ *   totals4[2] = sum RHO_H2O*(precip_liq_surf+precip_ice_surf)*dt     water that left through the surface
+ *   totals4[3] = sum RHO_H2O*LatIce*precip_liq_surf*dt                energy that left through the surface
+ * following the column formulas of share/property_checks/mass_and_energy_column_conservation_check.cpp:283-363
+ * (kinetic and geopotential terms omitted: p3_main cannot change them).  Call it before p3b200_main (with
+ * precip_*_surf zeroed) and after; conservation means  after[0]+after[2] == before[0]  and
+ * after[1]+after[3] == before[1]  up to rounding.  Asynchronous on cuda_stream when totals4_host == NULL
+ * (result in totals4_dev); with totals4_host != NULL it also copies the result back and synchronises. */
+int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
+                               void* cuda_stream, double* totals4_dev, double* totals4_host);
+
 /* ---- the reference's own C bridge, re-implemented on the GPU ---------------------------------------
  * Drop-in for p3_main_f (p3_functions_f90.hpp:945-952; p3_functions_f90.cpp:1888-2103): HOST pointers,
  * Fortran (column-major) layout arr[i + ncol*k], 1-based its/kts (must be 1), outputs zeroed on entry.

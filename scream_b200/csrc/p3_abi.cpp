@@ -67,6 +67,8 @@ struct p3b200_ctx {
   Slot slots[NSLOT];
   LaunchConfig cfg{};
   int cfg_nk = -1, cfg_ncol = -1;
+  double* d_budget = nullptr;     // [budget_cols][4] per-column values + BUDGET_PARTS*4 partials + 4 totals
+  size_t budget_cols = 0;
 };
 
 namespace {
@@ -232,6 +234,7 @@ int p3b200_destroy(p3b200_handle h) {
   if (h->d_tables) cudaFree(h->d_tables);
   if (h->d_diag) cudaFree(h->d_diag);
   if (h->d_queue) cudaFree(h->d_queue);
+  if (h->d_budget) cudaFree(h->d_budget);
   delete h;
   return P3B200_OK;
 }
@@ -305,6 +308,50 @@ int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches) {
   }
   *ms = total;
   if (launches) *launches = (int64_t)h->events_used;
+  return P3B200_OK;
+}
+
+}  // extern "C"
+
+namespace {
+template <typename Real>
+int budget_impl(p3b200_ctx* h, const P3B200Fields* f, const P3B200Infra* in, cudaStream_t stream, double* totals_dev) {
+  MainArgs<Real> a{};
+  for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<Real*>(f->ptr[i]); a.stride[i] = f->col_stride[i]; }
+  a.ncol = in->ncol; a.nk = in->nlev; a.dt = Real(in->dt);
+  double* col_vals = h->d_budget;
+  double* partials = h->d_budget + h->budget_cols * 4;
+  const int rc = launch_budget<Real>(a, col_vals, partials, BUDGET_PARTS, totals_dev, stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "budget launches");
+  return P3B200_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
+                               void* cuda_stream, double* totals4_dev, double* totals4_host) {
+  if (!h || !fields || !infra || infra->ncol < 0 || infra->nlev < 1) return P3B200_EINVAL;
+  static const int need[] = {P3B200_F_QV, P3B200_F_QC, P3B200_F_QI, P3B200_F_QR, P3B200_F_TH, P3B200_F_INV_EXNER,
+                             P3B200_F_DPRES, P3B200_F_PRECIP_LIQ_SURF, P3B200_F_PRECIP_ICE_SURF};
+  for (int i : need) if (!fields->ptr[i]) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  if (h->budget_cols < (size_t)infra->ncol || !h->d_budget) {
+    if (h->d_budget) { CU(cudaDeviceSynchronize()); CU(cudaFree(h->d_budget)); h->d_budget = nullptr; }
+    const size_t cols = infra->ncol > 0 ? (size_t)infra->ncol : 1;
+    CU(cudaMalloc(&h->d_budget, (cols * 4 + BUDGET_PARTS * 4 + 4) * sizeof(double)));
+    h->budget_cols = cols;
+  }
+  double* own = h->d_budget + h->budget_cols * 4 + BUDGET_PARTS * 4;
+  double* dst = totals4_dev ? totals4_dev : own;
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  const int rc = h->real_bytes == 8 ? budget_impl<double>(h, fields, infra, stream, dst)
+                                    : budget_impl<float>(h, fields, infra, stream, dst);
+  if (rc) return rc;
+  if (totals4_host) {
+    CU(cudaMemcpyAsync(totals4_host, dst, 4 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CU(cudaStreamSynchronize(stream));
+  }
   return P3B200_OK;
 }
 

@@ -27,5 +27,11 @@ constexpr int NUM_PHASE_MARKS = 6;
 template <typename Real>
 int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks);
 
+// Water/energy budget (p3_budget.cu): per-column values into col_vals[ncol][4], fixed-order two-level sum into
+// totals4 (device).  `partials` holds nparts*4 doubles of scratch.  Returns a cudaError_t as int.
+constexpr int BUDGET_PARTS = 256;
+template <typename Real>
+int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, int nparts, double* totals4, void* stream);
+
 }  // namespace p3b200
 #endif

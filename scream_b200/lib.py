@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
-    "p3b200_set_default_tables",
+    "p3b200_water_energy_totals", "p3b200_set_default_tables",
     "p3b200_p3_main_f",
 ]
 
@@ -92,6 +92,8 @@ def lib():
         L.p3b200_last_kernel_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
                                             ctypes.POINTER(ctypes.c_int64)]
         L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
+        L.p3b200_water_energy_totals.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
+                                                 ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
         L.p3b200_tables_read_text.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
         L.p3b200_tables_read_blob.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
@@ -223,6 +225,17 @@ class P3Handle:
                                      ctypes.byref(infra), ctypes.byref(us),
                                      diag.ctypes.data if want_diag else None), "p3b200_main_host")
         return us.value, diag
+
+    def water_energy_totals(self, fields, dt, stream=None):
+        """Domain totals [water, energy, surface water out, surface energy out] of a dict of device tensors
+        (p3b200_water_energy_totals); returns a numpy array of 4 doubles."""
+        f, ncol, nlev = self.fields_struct(fields, host=False)
+        infra = self._infra(ncol, nlev, dt, True, True, True)
+        out = np.zeros(4, dtype=np.float64)
+        check(lib().p3b200_water_energy_totals(self._h, ctypes.byref(f), ctypes.byref(infra),
+                                               ctypes.c_void_p(stream) if stream else None, None, out.ctypes.data),
+              "p3b200_water_energy_totals")
+        return out
 
     def get_diag(self, ncol):
         out = np.empty((ncol, NUM_DIAG), dtype=np.int32)
