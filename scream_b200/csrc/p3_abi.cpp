@@ -76,7 +76,7 @@ namespace {
 template <typename Real>
 int upload_tables(p3b200_ctx* h, const P3B200Tables& t) {
   const size_t n_ice = 12000, n_coll = 60000, n_v = 3000;
-  const size_t total = n_ice + n_coll + 3 * n_v;
+  const size_t total = n_ice + n_coll + 3 * n_v + 2 * n_v;
   std::vector<Real> host(total);
   size_t o = 0;
   const double* src = &t.ice_table_vals[0][0][0][0];
@@ -90,10 +90,17 @@ int upload_tables(p3b200_ctx* h, const P3B200Tables& t) {
     for (size_t i = 0; i < n_v; ++i) host[o + i] = Real(vs[v][i]);
     o += n_v;
   }
+  // (vm, vn) interleaved, one slice per mu_r column: [10][300][2]
+  for (int j = 0; j < 10; ++j)
+    for (int i = 0; i < 300; ++i) {
+      host[o + (size_t)(j * 300 + i) * 2 + 0] = Real(t.vm_table_vals[i][j]);
+      host[o + (size_t)(j * 300 + i) * 2 + 1] = Real(t.vn_table_vals[i][j]);
+    }
   CU(cudaMalloc(&h->d_tables, total * sizeof(Real)));
   CU(cudaMemcpy(h->d_tables, host.data(), total * sizeof(Real), cudaMemcpyHostToDevice));
   const Real* base = static_cast<const Real*>(h->d_tables);
-  Tables<Real> tb{base, base + n_ice, base + n_ice + n_coll, base + n_ice + n_coll + n_v, base + n_ice + n_coll + 2 * n_v};
+  Tables<Real> tb{base, base + n_ice, base + n_ice + n_coll, base + n_ice + n_coll + n_v, base + n_ice + n_coll + 2 * n_v,
+                  base + n_ice + n_coll + 3 * n_v};
   if constexpr (sizeof(Real) == 8) h->tbd = tb; else h->tbf = tb;
   return P3B200_OK;
 }

@@ -57,7 +57,6 @@ enum DiagId {
 enum Species { SP_CLOUD = 0, SP_RAIN = 1, SP_ICE = 2 };
 
 constexpr int MAX_NLEV = 256;
-constexpr int HIST_ROWS = 3;        // phase A parks the three history outputs of a column in shared memory
 
 // Kernel arguments (by value in param space).
 template <typename Real>
@@ -73,179 +72,273 @@ struct MainArgs {
   unsigned int* queue;     // work-queue counters, one per sedimentation launch (species x window class), zeroed before phase A
 };
 
-// lane-private bit set indexed by level slot (k / WP::size)
-template <int NWORDS>
-struct LaneBits {
-  unsigned w[NWORDS];
-  P3_HD void clear() { for (int i = 0; i < NWORDS; ++i) w[i] = 0u; }
-  P3_HD void set(int j) { w[j >> 5] |= (1u << (j & 31)); }
-  P3_HD bool get(int j) const { return (w[j >> 5] >> (j & 31)) & 1u; }
-};
-
 template <typename Real>
 P3_HD Real* col_ptr(const MainArgs<Real>& a, int f, int64_t col) { return a.f[f] + col * a.stride[f]; }
 
 // =================================================================================================
 // Phase A: p3_main_init (p3_main_impl.hpp:21-72) + p3_main_part1 (p3_main_impl_part1.hpp:21-185) +
-// p3_main_part2 (p3_main_impl_part2.hpp:21-526) for one column; `hist` = HIST_ROWS*nk Reals of scratch.
-template <typename Real, typename WP>
+// p3_main_part2 (p3_main_impl_part2.hpp:21-526).  All three are level-local, so phase A is written per
+// LEVEL and the kernel is free to choose which lane runs which level:
+//
+//   pass 1 (every level, one thread per level, coalesced along the column): init + the part of part1
+//          that decides the column flags (nucleationPossible, hydrometeorsPresent) and the level's
+//          skip_all gate (p3_main_impl_part2.hpp:121-127).  A skip_all level is COMPLETE after part1 —
+//          its post-part1 state is stored here from 7 loads.  Any other level is only classified: the
+//          pass returns a sort key (which species are present, temperature regime) and stores nothing.
+//   pass 2 (the classified levels, sorted by key so that the 32 lanes of a warp run the same process
+//          branches): init + part1 + part2 from the level's untouched inputs, stores, and the
+//          per-column reductions (hydrometeorsPresent after part2, find_top/find_bottom of the three
+//          sedimenting species) into a small per-column accumulator.
+//
+// The accumulator `acc` is COL_ACC_N ints per column; AT is the access policy (shared-memory atomics in
+// the kernel, plain stores in the host build of this source).
+enum ColAcc { CA_FLAGS = 0, CA_LO_C, CA_HI_C, CA_LO_R, CA_HI_R, CA_LO_I, CA_HI_I, COL_ACC_N };
+enum ColFlag { CF_NUC = 1, CF_HYD1 = 2, CF_HYD2 = 4, CF_ERR_SHIFT = 8 };
+constexpr int A_NKEYS = 32;
+
+struct AccPlain {
+  static P3_HD void or_(int* p, int v) { *p |= v; }
+  static P3_HD void min_(int* p, int v) { if (v < *p) *p = v; }
+  static P3_HD void max_(int* p, int v) { if (v > *p) *p = v; }
+};
+
+template <typename Real>
 struct PhaseA {
   using P = Phys<Real>;
   using C = Cst<Real>;
-  static constexpr int WS = WP::size;
   static P3_HD Real sp(double x) { return static_cast<Real>(x); }
 
-  static P3_HD void run(const WP& w, const MainArgs<Real>& a, int64_t col, Real* hist) {
-    const int lane = w.lane();
-    const int nk = a.nk;
+  static P3_HD void acc_init(int* acc) {
+    acc[CA_FLAGS] = 0;
+    acc[CA_LO_C] = MAX_NLEV + 1; acc[CA_HI_C] = -1; acc[CA_LO_R] = MAX_NLEV + 1; acc[CA_HI_R] = -1;
+    acc[CA_LO_I] = MAX_NLEV + 1; acc[CA_HI_I] = -1;
+  }
+
+  // ---- pass 1 -----------------------------------------------------------------------------------
+  struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres; };
+  static P3_HD void pass1_load(const MainArgs<Real>& a, int64_t col, int k, In1& in) {
+    in.qc = col_ptr(a, F_QC, col)[k]; in.qr = col_ptr(a, F_QR, col)[k]; in.qi = col_ptr(a, F_QI, col)[k];
+    in.qv = col_ptr(a, F_QV, col)[k]; in.th = col_ptr(a, F_TH, col)[k];
+    in.inv_exner = P3_LDG(col_ptr(a, F_INV_EXNER, col) + k);
+    in.pres = P3_LDG(col_ptr(a, F_PRES, col) + k);
+  }
+
+  // Single-precision estimate of qv / qv_sat_i(T0, pres) on a cold level (relative error < 1e-4: fp32
+  // rounding of the Murphy-Koop ice exponent, |terms| <= 40, plus the fast exp/log).  Pass 1 only needs the
+  // three DECISIONS the reference takes on qv_supersat_i (>= -0.05: nucleationPossible and skip_all; < -0.1:
+  // small-ice clipping); when the estimate is further than 2e-3 from every threshold that matters the decision
+  // is already certain and the fp64 evaluation is skipped.  Returns false when the exact value is needed.
+  static P3_HD bool supersat_decided(Real T0, Real pres, Real qv0, bool small_ice, Real& supersat_i) {
+    if constexpr (sizeof(Real) == 8) {
+      const float Tf = (float)T0;
+#if defined(__CUDA_ARCH__)
+      const float e = __expf(9.550426f - __fdividef(5723.265f, Tf) + 3.53068f * __logf(Tf) - 0.00728332f * Tf);
+#else
+      const float e = std::exp(9.550426f - 5723.265f / Tf + 3.53068f * std::log(Tf) - 0.00728332f * Tf);
+#endif
+      const float ratio = (float)qv0 * fmaxf((float)pres, 1.e-3f) / ((float)C::ep_2 * e);
+      const bool clear95 = fabsf(ratio - 0.95f) > 2.e-3f;
+      const bool clear90 = !small_ice || fabsf(ratio - 0.90f) > 2.e-3f;
+      if (clear95 && clear90 && ratio < 1.e30f) {     // NaN/inf estimates fall through to the exact path
+        supersat_i = (Real)ratio - 1;
+        return true;
+      }
+      return false;
+    } else {
+      return false;
+    }
+  }
+
+  // Returns -1 when the level is finished (skip_all; state stored), else its sort key in [0, A_NKEYS).
+  // `flags` receives CF_NUC / CF_HYD1 / error bits of this level (to be OR-ed into the column's accumulator).
+  static P3_HD int pass1_level(const MainArgs<Real>& a, int64_t col, int k, const In1& in, int& flags) {
+    const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
+    Real qc = in.qc, qr = in.qr, qi = in.qi, qv = in.qv, th = in.th;
+    const Real inv_exner = in.inv_exner;
+    // p3_main_init
+    const Real exner = 1 / inv_exner;
+    const Real T0 = th * exner;
+    qv = P::rmax(qv, 0);
+    int err = P::check_temperature(T0);
+    const bool cold0 = T0 < Tz;
+    // qv_supersat_i (p3_main_impl_part1.hpp:95-101) is consumed by nucleationPossible on cold levels, by the
+    // small-ice clipping when qi is in [qsmall, 1e-8) and by skip_all; evaluated only where one of them asks
+    const Real qv0 = qv;
+    const bool small_ice = qi >= qsmall && qi < sp(1.e-8);
+    Real supersat_i = 0;
+    bool have_sat = false;
+    auto eval_sat = [&]() {
+      const Real logT0 = P::x_log(T0);
+      const Real svp = cold0 ? P::svp_ice(T0, logT0) : P::svp_liquid(T0, logT0);
+      supersat_i = qv0 / P::qv_from_svp(svp, in.pres) - 1;
+      have_sat = true;
+    };
+    if (cold0) {
+      if (supersat_decided(T0, in.pres, qv0, small_ice, supersat_i)) have_sat = true;
+      else eval_sat();
+    } else if (small_ice) {
+      eval_sat();
+    }
+    flags = 0;
+    if (cold0 && supersat_i >= sp(-0.05)) flags |= CF_NUC;
+    if (qc < qsmall) { qv = qv + qc; th = th - inv_exner * qc * latvap * inv_cp; qc = 0; } else flags |= CF_HYD1;
+    if (qr < qsmall) { qv = qv + qr; th = th - inv_exner * qr * latvap * inv_cp; qr = 0; } else flags |= CF_HYD1;
+    if (qi < qsmall || (qi < sp(1.e-8) && supersat_i < sp(-0.1))) {
+      qv = qv + qi; th = th - inv_exner * qi * (latvap + latice) * inv_cp; qi = 0;
+    } else flags |= CF_HYD1;
+    if (qi >= qsmall && qi < sp(1.e-8) && T0 >= Tz) {
+      qr = qr + qi; th = th - inv_exner * qi * latice * inv_cp; qi = 0;
+    }
+    const Real T = th * exner;
+    const bool has_c = qc >= qsmall, has_r = qr >= qsmall, has_i = qi >= qsmall;
+    bool skip_all = !has_c && !has_r && !has_i && T < Tz;
+    if (skip_all) {
+      if (!have_sat) eval_sat();          // T0 >= Tmelt but the clipped level is colder: rare
+      skip_all = supersat_i < sp(-0.05);
+    }
+    flags |= err << CF_ERR_SHIFT;
+    if (!skip_all) {
+      const int tcls = (T <= C::T_rainfrz) ? 2 : (T < Tz) ? 1 : 0;
+      return (int(has_i) << 4) | (int(has_r) << 3) | (int(has_c) << 2) | tcls;
+    }
+    // the level is complete: every hydrometeor was clipped into vapour (p3_main_impl_part1.hpp:123-175),
+    // part2 does not run (p3_main_impl.hpp:211-217: its outputs stay zero)
+    col_ptr(a, F_QC, col)[k] = 0; col_ptr(a, F_NC, col)[k] = 0; col_ptr(a, F_QR, col)[k] = 0; col_ptr(a, F_NR, col)[k] = 0;
+    col_ptr(a, F_QI, col)[k] = 0; col_ptr(a, F_QM, col)[k] = 0; col_ptr(a, F_NI, col)[k] = 0; col_ptr(a, F_BM, col)[k] = 0;
+    col_ptr(a, F_QV, col)[k] = qv; col_ptr(a, F_TH, col)[k] = th;
+    col_ptr(a, F_QV2QI_DEPOS_TEND, col)[k] = 0; col_ptr(a, F_PRECIP_TOTAL_TEND, col)[k] = 0; col_ptr(a, F_NEVAPR, col)[k] = 0;
+    col_ptr(a, F_PRECIP_LIQ_FLUX, col)[k] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[k] = 0;
+    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = (T < C::T_homogfrz) ? -T0 : T0;
+    return -1;
+  }
+
+  // ---- pass 2 -----------------------------------------------------------------------------------
+  // `col_active` = nucleationPossible || hydrometeorsPresent of the column (known after pass 1).
+  template <class AT>
+  static P3_HD void pass2_level(const MainArgs<Real>& a, int64_t col, int k, bool col_active, int* acc) {
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
     const Real dt = a.dt, inv_dt = 1 / a.dt;
     const bool predictNc = a.predictNc != 0, prescribedCCN = a.prescribedCCN != 0;
+    Real* const g_qc = col_ptr(a, F_QC, col) + k; Real* const g_nc = col_ptr(a, F_NC, col) + k;
+    Real* const g_qr = col_ptr(a, F_QR, col) + k; Real* const g_nr = col_ptr(a, F_NR, col) + k;
+    Real* const g_qi = col_ptr(a, F_QI, col) + k; Real* const g_qm = col_ptr(a, F_QM, col) + k;
+    Real* const g_ni = col_ptr(a, F_NI, col) + k; Real* const g_bm = col_ptr(a, F_BM, col) + k;
+    Real* const g_qv = col_ptr(a, F_QV, col) + k; Real* const g_th = col_ptr(a, F_TH, col) + k;
 
-    Real* const g_qc = col_ptr(a, F_QC, col); Real* const g_nc = col_ptr(a, F_NC, col);
-    Real* const g_qr = col_ptr(a, F_QR, col); Real* const g_nr = col_ptr(a, F_NR, col);
-    Real* const g_qi = col_ptr(a, F_QI, col); Real* const g_qm = col_ptr(a, F_QM, col);
-    Real* const g_ni = col_ptr(a, F_NI, col); Real* const g_bm = col_ptr(a, F_BM, col);
-    Real* const g_qv = col_ptr(a, F_QV, col); Real* const g_th = col_ptr(a, F_TH, col);
-    const Real* const g_cfi = col_ptr(a, F_CLD_FRAC_I, col); const Real* const g_cfl = col_ptr(a, F_CLD_FRAC_L, col);
-    const Real* const g_cfr = col_ptr(a, F_CLD_FRAC_R, col); const Real* const g_pres = col_ptr(a, F_PRES, col);
-    const Real* const g_dz = col_ptr(a, F_DZ, col); const Real* const g_dpres = col_ptr(a, F_DPRES, col);
-    const Real* const g_inv_exner = col_ptr(a, F_INV_EXNER, col);
-    const Real* const g_qv_prev = col_ptr(a, F_QV_PREV, col); const Real* const g_t_prev = col_ptr(a, F_T_PREV, col);
-    const Real* const g_nccn = a.f[F_NCCN] ? col_ptr(a, F_NCCN, col) : nullptr;
-    const Real* const g_nc_nuceat = a.f[F_NC_NUCEAT_TEND] ? col_ptr(a, F_NC_NUCEAT_TEND, col) : nullptr;
-    const Real* const g_ni_act = a.f[F_NI_ACTIVATED] ? col_ptr(a, F_NI_ACTIVATED, col) : nullptr;
-    Real* const g_plf = col_ptr(a, F_PRECIP_LIQ_FLUX, col); Real* const g_pif = col_ptr(a, F_PRECIP_ICE_FLUX, col);
-    Real* const g_depos = col_ptr(a, F_QV2QI_DEPOS_TEND, col); Real* const g_ptt = col_ptr(a, F_PRECIP_TOTAL_TEND, col);
-    Real* const g_nevapr = col_ptr(a, F_NEVAPR, col);
-    Real* const g_stash = col_ptr(a, F_DIAG_EFF_RADIUS_QC, col);
-    Real* const h_lie = hist; Real* const h_vle = hist + nk; Real* const h_vie = hist + 2 * nk;
+    typename P::Level L;
+    L.qc = *g_qc; L.nc = *g_nc; L.qr = *g_qr; L.nr = *g_nr; L.qi = *g_qi;
+    L.qm = *g_qm; L.ni = *g_ni; L.bm = *g_bm; L.qv = *g_qv; L.th = *g_th;
+    L.pres = P3_LDG(col_ptr(a, F_PRES, col) + k); L.inv_exner = P3_LDG(col_ptr(a, F_INV_EXNER, col) + k);
+    L.cf_i = P3_LDG(col_ptr(a, F_CLD_FRAC_I, col) + k); L.cf_l = P3_LDG(col_ptr(a, F_CLD_FRAC_L, col) + k);
+    L.cf_r = P3_LDG(col_ptr(a, F_CLD_FRAC_R, col) + k);
+    const Real dz = P3_LDG(col_ptr(a, F_DZ, col) + k), dpres = P3_LDG(col_ptr(a, F_DPRES, col) + k);
+    // p3_main_init: p3_main_impl.hpp:21-72
+    L.inv_cf_i = 1 / L.cf_i; L.inv_cf_l = 1 / L.cf_l; L.inv_cf_r = 1 / L.cf_r;
+    const Real exner = 1 / L.inv_exner;
+    const Real T0 = L.th * exner;
+    L.qv = P::rmax(L.qv, 0);
+    // p3_main_part1: p3_main_impl_part1.hpp:89-182
+    L.rho = dpres / dz / C::gravit;
+    L.inv_rho = 1 / L.rho;
+    int err = P::check_temperature(T0);
+    const Real logT0 = P::x_log(T0);
+    const bool cold0 = T0 < Tz;
+    const Real svp_l = P::svp_liquid(T0, logT0);
+    L.qv_sat_l = P::qv_from_svp(svp_l, L.pres);
+    L.qv_sat_i = cold0 ? P::qv_from_svp(P::svp_ice(T0, logT0), L.pres) : L.qv_sat_l;
+    L.qv_supersat_i = L.qv / L.qv_sat_i - 1;
 
-    int err = 0;
-    bool nuc = false, hyd1 = false, hyd2 = false;
-    // find_top / find_bottom (p3_find_impl.hpp) of the three sedimenting species on the post-part2
-    // state, accumulated per lane and reduced once per column
-    int lo_c = MAX_NLEV + 1, hi_c = -1, lo_r = MAX_NLEV + 1, hi_r = -1, lo_i = MAX_NLEV + 1, hi_i = -1;
-    LaneBits<(MAX_NLEV / WS + 31) / 32> p2;   // per level slot of this lane: the level ran part2
-    p2.clear();
-
-    int slot = 0;
-    for (int k = lane; k < nk; k += WS, ++slot) {
-      typename P::Level L;
-      L.qc = g_qc[k]; L.nc = g_nc[k]; L.qr = g_qr[k]; L.nr = g_nr[k]; L.qi = g_qi[k];
-      L.qm = g_qm[k]; L.ni = g_ni[k]; L.bm = g_bm[k]; L.qv = g_qv[k]; L.th = g_th[k];
-      L.pres = P3_LDG(g_pres + k); L.inv_exner = P3_LDG(g_inv_exner + k);
-      L.cf_i = P3_LDG(g_cfi + k); L.cf_l = P3_LDG(g_cfl + k); L.cf_r = P3_LDG(g_cfr + k);
-      const Real dz = P3_LDG(g_dz + k), dpres = P3_LDG(g_dpres + k);
-      // p3_main_init: p3_main_impl.hpp:21-72
-      L.inv_cf_i = 1 / L.cf_i; L.inv_cf_l = 1 / L.cf_l; L.inv_cf_r = 1 / L.cf_r;
-      const Real exner = 1 / L.inv_exner;
-      const Real T0 = L.th * exner;
-      L.qv = P::rmax(L.qv, 0);
-      // p3_main_part1: p3_main_impl_part1.hpp:89-182
-      L.rho = dpres / dz / C::gravit;
-      L.inv_rho = 1 / L.rho;
-      err |= P::check_temperature(T0);
-      const Real logT0 = std::log(T0);
-      const bool cold0 = T0 < Tz;
-      Real svp_l = 0;
-      bool have_svp_l = false;
-      if (!cold0) { svp_l = P::svp_liquid(T0, logT0); have_svp_l = true; }
-      L.qv_sat_i = P::qv_from_svp(cold0 ? P::svp_ice(T0, logT0) : svp_l, L.pres);
-      L.qv_supersat_i = L.qv / L.qv_sat_i - 1;
-      if (cold0 && L.qv_supersat_i >= sp(-0.05)) nuc = true;
-
-      if (L.qc < qsmall) {
-        L.qv = L.qv + L.qc;
-        L.th = L.th - L.inv_exner * L.qc * latvap * inv_cp;
-        L.qc = 0; L.nc = 0;
-      } else {
-        hyd1 = true;
-        if (prescribedCCN)  L.nc = P::rmax(L.nc, a.ro.spa_ccn_to_nc_factor * P3_LDG(g_nccn + k) / L.inv_cf_l);
-        else if (predictNc) L.nc = P::rmax(L.nc + P3_LDG(g_nc_nuceat + k) * dt, sp(0.0));
-        else                L.nc = C::NCCNST * L.inv_rho;
-      }
-      if (L.qr < qsmall) {
-        L.qv = L.qv + L.qr;
-        L.th = L.th - L.inv_exner * L.qr * latvap * inv_cp;
-        L.qr = 0; L.nr = 0;
-      } else hyd1 = true;
-      if (L.qi < qsmall || (L.qi < sp(1.e-8) && L.qv_supersat_i < sp(-0.1))) {
-        L.qv = L.qv + L.qi;
-        L.th = L.th - L.inv_exner * L.qi * (latvap + latice) * inv_cp;
-        L.qi = 0; L.ni = 0; L.qm = 0; L.bm = 0;
-      } else hyd1 = true;
-      if (L.qi >= qsmall && L.qi < sp(1.e-8) && T0 >= Tz) {
-        L.qr = L.qr + L.qi;
-        L.th = L.th - L.inv_exner * L.qi * latice * inv_cp;
-        L.qi = 0; L.ni = 0; L.qm = 0; L.bm = 0;
-      }
-      L.T = L.th * exner;
-      L.T_init = T0;
-      const bool frz = L.T < C::T_homogfrz;
-
-      // p3_main_part2 (p3_main_impl_part2.hpp:121-127: skip_all)
-      Real o_depos = 0, o_ptt = 0, o_nevapr = 0;
-      const bool skip_all = (L.qc < qsmall && L.qr < qsmall && L.qi < qsmall && L.T < Tz && L.qv_supersat_i < sp(-0.05));
-      if (!skip_all) {
-        if (!have_svp_l) svp_l = P::svp_liquid(T0, logT0);
-        L.qv_sat_l = P::qv_from_svp(svp_l, L.pres);
-        typename P::Part2Out o;
-        const bool h = P::part2_level(L, a.tb, a.ro, dt, inv_dt, predictNc, prescribedCCN,
-                                      g_qv_prev + k, g_t_prev + k, g_ni_act ? g_ni_act + k : nullptr, o, err);
-        if (h) hyd2 = true;
-        p2.set(slot);
-        o_depos = o.qv2qi_depos_tend; o_ptt = o.precip_total_tend; o_nevapr = o.nevapr;
-        h_lie[k] = o.liq_ice_exchange; h_vle[k] = o.vap_liq_exchange; h_vie[k] = o.vap_ice_exchange;
-      }
-      if (L.qc >= qsmall) { if (k < lo_c) lo_c = k; hi_c = k; }
-      if (L.qr >= qsmall) { if (k < lo_r) lo_r = k; hi_r = k; }
-      if (L.qi >= qsmall) { if (k < lo_i) lo_i = k; hi_i = k; }
-      // the post-part2 state goes straight back to HBM
-      g_qc[k] = L.qc; g_nc[k] = L.nc; g_qr[k] = L.qr; g_nr[k] = L.nr; g_qi[k] = L.qi;
-      g_qm[k] = L.qm; g_ni[k] = L.ni; g_bm[k] = L.bm; g_qv[k] = L.qv; g_th[k] = L.th;
-      // outputs that are final after part2 (zero where part2 did not run: p3_main_impl.hpp:211-217)
-      g_depos[k] = o_depos; g_ptt[k] = o_ptt; g_nevapr[k] = o_nevapr;
-      g_plf[k] = 0; g_pif[k] = 0;
-      g_stash[k] = frz ? -T0 : T0;
+    if (L.qc < qsmall) {
+      L.qv = L.qv + L.qc;
+      L.th = L.th - L.inv_exner * L.qc * latvap * inv_cp;
+      L.qc = 0; L.nc = 0;
+    } else {
+      if (prescribedCCN)  L.nc = P::rmax(L.nc, a.ro.spa_ccn_to_nc_factor * P3_LDG(col_ptr(a, F_NCCN, col) + k) / L.inv_cf_l);
+      else if (predictNc) L.nc = P::rmax(L.nc + P3_LDG(col_ptr(a, F_NC_NUCEAT_TEND, col) + k) * dt, sp(0.0));
+      else                L.nc = C::NCCNST * L.inv_rho;
     }
-    if (a.zero_flux_top && lane == (nk % WS)) { g_plf[nk] = 0; g_pif[nk] = 0; }
+    if (L.qr < qsmall) {
+      L.qv = L.qv + L.qr;
+      L.th = L.th - L.inv_exner * L.qr * latvap * inv_cp;
+      L.qr = 0; L.nr = 0;
+    }
+    if (L.qi < qsmall || (L.qi < sp(1.e-8) && L.qv_supersat_i < sp(-0.1))) {
+      L.qv = L.qv + L.qi;
+      L.th = L.th - L.inv_exner * L.qi * (latvap + latice) * inv_cp;
+      L.qi = 0; L.ni = 0; L.qm = 0; L.bm = 0;
+    }
+    if (L.qi >= qsmall && L.qi < sp(1.e-8) && T0 >= Tz) {
+      L.qr = L.qr + L.qi;
+      L.th = L.th - L.inv_exner * L.qi * latice * inv_cp;
+      L.qi = 0; L.ni = 0; L.qm = 0; L.bm = 0;
+    }
+    L.T = L.th * exner;
+    L.T_init = T0;
+    const bool frz = L.T < C::T_homogfrz;
 
-    nuc = w.any(nuc); hyd1 = w.any(hyd1); hyd2 = w.any(hyd2);
+    // p3_main_part2 (this level is not skip_all: pass 1 decided that on the same values)
+    typename P::Part2Out o;
+    const Real* const g_ni_act = a.f[F_NI_ACTIVATED] ? col_ptr(a, F_NI_ACTIVATED, col) + k : nullptr;
+    const bool h = P::part2_level(L, a.tb, a.ro, dt, inv_dt, predictNc, prescribedCCN,
+                                  col_ptr(a, F_QV_PREV, col) + k, col_ptr(a, F_T_PREV, col) + k, g_ni_act, o, err);
+    int fl = (h ? CF_HYD2 : 0) | (err << CF_ERR_SHIFT);
+    if (fl) AT::or_(acc + CA_FLAGS, fl);
+    // find_top / find_bottom (p3_find_impl.hpp) of the sedimenting species on the post-part2 state
+    if (L.qc >= qsmall) { AT::min_(acc + CA_LO_C, k); AT::max_(acc + CA_HI_C, k); }
+    if (L.qr >= qsmall) { AT::min_(acc + CA_LO_R, k); AT::max_(acc + CA_HI_R, k); }
+    if (L.qi >= qsmall) { AT::min_(acc + CA_LO_I, k); AT::max_(acc + CA_HI_I, k); }
+    *g_qc = L.qc; *g_nc = L.nc; *g_qr = L.qr; *g_nr = L.nr; *g_qi = L.qi;
+    *g_qm = L.qm; *g_ni = L.ni; *g_bm = L.bm; *g_qv = L.qv; *g_th = L.th;
+    col_ptr(a, F_QV2QI_DEPOS_TEND, col)[k] = o.qv2qi_depos_tend;
+    col_ptr(a, F_PRECIP_TOTAL_TEND, col)[k] = o.precip_total_tend;
+    col_ptr(a, F_NEVAPR, col)[k] = o.nevapr;
+    col_ptr(a, F_PRECIP_LIQ_FLUX, col)[k] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[k] = 0;
+    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = frz ? -T0 : T0;
+    // history arrays are only touched where part2 ran (p3_main_impl_part2.hpp:468-470), and part2 only runs
+    // for columns that can nucleate or hold hydrometeors after part1 (p3_main_impl.hpp:237); for any other
+    // column all tendencies of this level are exactly zero and the prognostics above are unchanged
+    if (col_active) {
+      col_ptr(a, F_LIQ_ICE_EXCHANGE, col)[k] = o.liq_ice_exchange;
+      col_ptr(a, F_VAP_LIQ_EXCHANGE, col)[k] = o.vap_liq_exchange;
+      col_ptr(a, F_VAP_ICE_EXCHANGE, col)[k] = o.vap_ice_exchange;
+    }
+  }
+
+  // ---- per column, after both passes: flags and sedimentation ranges into the integer diagnostics
+  static P3_HD void finish_column(const MainArgs<Real>& a, int64_t col, const int* acc) {
+    const int fl = acc[CA_FLAGS];
+    const bool nuc = fl & CF_NUC, hyd1 = fl & CF_HYD1, hyd2 = fl & CF_HYD2;
     const bool active = nuc || hyd1;
     const bool full = active && hyd2;
-    // history arrays are only touched where part2 ran (p3_main_impl_part2.hpp:468-470)
-    {
-      Real* lie = col_ptr(a, F_LIQ_ICE_EXCHANGE, col); Real* vle = col_ptr(a, F_VAP_LIQ_EXCHANGE, col);
-      Real* vie = col_ptr(a, F_VAP_ICE_EXCHANGE, col);
-      slot = 0;
-      for (int k = lane; k < nk; k += WS, ++slot) {
-        if (active && p2.get(slot)) { lie[k] = h_lie[k]; vle[k] = h_vle[k]; vie[k] = h_vie[k]; }
-      }
+    a.f[F_PRECIP_LIQ_SURF][col] = 0;
+    a.f[F_PRECIP_ICE_SURF][col] = 0;
+    if (a.zero_flux_top) { col_ptr(a, F_PRECIP_LIQ_FLUX, col)[a.nk] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[a.nk] = 0; }
+    int* d = a.diag + col * D_NUM;
+    d[D_NUC_POSSIBLE] = nuc; d[D_HYDRO_PART1] = hyd1; d[D_HYDRO_PART2] = active ? (int)hyd2 : -1;
+    const bool c = full && acc[CA_HI_C] >= 0, r = full && acc[CA_HI_R] >= 0, i = full && acc[CA_HI_I] >= 0;
+    d[D_QC_KTOP] = c ? acc[CA_LO_C] : -1; d[D_QC_KBOT] = c ? acc[CA_HI_C] : -1; d[D_QC_NSUB] = 0;
+    d[D_QR_KTOP] = r ? acc[CA_LO_R] : -1; d[D_QR_KBOT] = r ? acc[CA_HI_R] : -1; d[D_QR_NSUB] = 0;
+    d[D_QI_KTOP] = i ? acc[CA_LO_I] : -1; d[D_QI_KBOT] = i ? acc[CA_HI_I] : -1; d[D_QI_NSUB] = 0;
+    d[D_ERROR] = fl >> CF_ERR_SHIFT; d[13] = -1; d[14] = -1; d[15] = -1;
+  }
+
+  // Host build only (tests/hostsim): the two passes for one column in the order the kernel runs them.
+  static inline void run_column_host(const MainArgs<Real>& a, int64_t col) {
+    int acc[COL_ACC_N];
+    acc_init(acc);
+    int keys[MAX_NLEV];
+    for (int k = 0; k < a.nk; ++k) {
+      int fl = 0;
+      In1 in;
+      pass1_load(a, col, k, in);
+      keys[k] = pass1_level(a, col, k, in, fl);
+      acc[CA_FLAGS] |= fl;
     }
-    if (!full) {   // the column leaves p3_main here (p3_main_impl.hpp:237,258): part3 outputs keep their defaults
-      Real* const o_rqc = col_ptr(a, F_DIAG_EFF_RADIUS_QC, col); Real* const o_rqi = col_ptr(a, F_DIAG_EFF_RADIUS_QI, col);
-      Real* const o_rqr = col_ptr(a, F_DIAG_EFF_RADIUS_QR, col); Real* const o_rho_qi = col_ptr(a, F_RHO_QI, col);
-      for (int k = lane; k < nk; k += WS) {
-        o_rqc[k] = sp(10.e-6); o_rqi[k] = sp(25.e-6); o_rqr[k] = sp(500.e-6); o_rho_qi[k] = 0;
-      }
-    }
-    lo_c = w.min_int(lo_c); hi_c = w.max_int(hi_c);
-    lo_r = w.min_int(lo_r); hi_r = w.max_int(hi_r);
-    lo_i = w.min_int(lo_i); hi_i = w.max_int(hi_i);
-    err = w.or_int(err);
-    if (lane == 0) {
-      a.f[F_PRECIP_LIQ_SURF][col] = 0;
-      a.f[F_PRECIP_ICE_SURF][col] = 0;
-      int* d = a.diag + col * D_NUM;
-      d[D_NUC_POSSIBLE] = nuc; d[D_HYDRO_PART1] = hyd1; d[D_HYDRO_PART2] = active ? (int)hyd2 : -1;
-      const bool c = full && hi_c >= 0, r = full && hi_r >= 0, i = full && hi_i >= 0;
-      d[D_QC_KTOP] = c ? lo_c : -1; d[D_QC_KBOT] = c ? hi_c : -1; d[D_QC_NSUB] = 0;
-      d[D_QR_KTOP] = r ? lo_r : -1; d[D_QR_KBOT] = r ? hi_r : -1; d[D_QR_NSUB] = 0;
-      d[D_QI_KTOP] = i ? lo_i : -1; d[D_QI_KBOT] = i ? hi_i : -1; d[D_QI_NSUB] = 0;
-      d[D_ERROR] = err; d[13] = -1; d[14] = -1; d[15] = -1;
-    }
-    w.sync();   // the history rows are reused by the next column of this warp
+    const bool active = (acc[CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
+    for (int key = A_NKEYS - 1; key >= 0; --key)
+      for (int k = 0; k < a.nk; ++k)
+        if (keys[k] == key) pass2_level<AccPlain>(a, col, k, active, acc);
+    finish_column(a, col, acc);
   }
 };
 
@@ -286,6 +379,7 @@ struct Sediment {
 #pragma unroll
     for (int j = 0; j < JW; ++j) {
       const int k = kw + lane + j * WS;
+      if (JW > 1 && kw + j * WS > k_temp) { flux[j] = 0; prev_last = 0; continue; }   // warp-uniform: slot below the front
       const bool in = k <= k_temp;
       const Real f = in ? V[j] * r[j] * rho[j] : Real(0);
       Real up = w.shfl_up1(f);
@@ -299,7 +393,9 @@ struct Sediment {
     }
   }
 
-  static P3_HD void run(const WP& w, const MainArgs<Real>& a, int64_t col, int k_qxtop, int k_qxbot) {
+  // rain_tab (rain only): the 300 x (vm, vn) slice of Tables::vmn for this run's mu_r column, or nullptr
+  static P3_HD void run(const WP& w, const MainArgs<Real>& a, int64_t col, int k_qxtop, int k_qxbot,
+                        const Real* rain_tab = nullptr) {
     const int lane = w.lane();
     const int nk = a.nk, kbot = nk - 1;
     const Real qsmall = C::QSMALL;
@@ -340,7 +436,7 @@ struct Sediment {
         } else if (SP == SP_RAIN) {
           fac[j] = std::pow(C::RHO_1000MB * inv_rho[j], sp(.54));   // rhofacr, p3_main_impl_part1.hpp:105
         } else {
-          fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54));    // rhofaci, p3_main_impl_part1.hpp:106
+          fac[j] = -1;    // rhofaci (p3_main_impl_part1.hpp:106) is evaluated when the level first holds ice
         }
       } else {
         q[j] = 0; n[j] = 0; rho[j] = 1; inv_rho[j] = 1; inv_dz[j] = 0; cf[j] = 1; icf[j] = 1; fac[j] = 0;
@@ -359,6 +455,12 @@ struct Sediment {
     const Real c_min = 1 / lamr_max, c_max = 1 / lamr_min;    // bounds on 1/lamr
     // nr = lamr^3 qr / mass_to_d3 at the two limiters (p3_dsd2_impl.hpp:116-119)
     const Real nr_per_q_min = lamr_min * lamr_min * lamr_min / mass_to_d3, nr_per_q_max = lamr_max * lamr_max * lamr_max / mass_to_d3;
+    // the mu_r axis of the fall-speed tables (p3_table3_impl.hpp:52-62) is the same on every level: when its
+    // interpolation weight is exactly 0 (integral mu_r) the bilinear form reduces bit for bit to the linear
+    // interpolation along the size axis, read from the (vm, vn)-interleaved slice `rain_tab`
+    typename P::Loc3 tj;
+    P::lookup3_from_dum1(mu_r, sp(0.0), tj);
+    const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr && (tj.rdumjj - Real(tj.dumjj)) == 0;
 
     while (dt_left > C::dt_left_tol) {
       const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
@@ -368,6 +470,7 @@ struct Sediment {
       for (int j = 0; j < JW; ++j) {
         const int k = kw + lane + j * WS;
         Real vq = 0, vn = 0;
+        if (JW > 1 && kw + j * WS > k_qxbot) { Vq[j] = 0; Vn[j] = 0; continue; }   // warp-uniform: the front has not reached this slot
         if (k <= k_qxbot) {
           if (SP == SP_CLOUD) {
             Real qc_i, nc_i;
@@ -396,10 +499,26 @@ struct Sediment {
               nr_i = nr_lim;
               if (c > c_max) { nr_i = qr_i * nr_per_q_min; c = c_max; }         // lamr < lammin
               else if (c < c_min) { nr_i = qr_i * nr_per_q_max; c = c_min; }    // lamr > lammax
-              typename P::Loc3 t3;
-              P::lookup3_from_dum1(mu_r, (mu_r + 1) * c, t3);
-              vq = P::apply_table3(a.tb.vm, t3) * fac[j];
-              vn = P::apply_table3(a.tb.vn, t3) * fac[j];
+              if (rain_fast) {
+                // lookup (p3_table3_impl.hpp:17-65) with selects instead of the two-regime branch
+                const Real dum1 = (mu_r + 1) * c;
+                const bool sm = dum1 <= sp(195.e-6);
+                const Real x = dum1 * sp(1.e6);
+                Real r = sm ? (x + 5) * sp(0.1) : (x - 195) * (C::THIRD * sp(0.1)) + 20;
+                r = P::rmax(r, sm ? sp(1.0) : sp(20.0));
+                r = P::rmin(r, sm ? sp(20.0) : sp(300.0));
+                int d = static_cast<int>(r);
+                d = P::imin(P::imax(d, sm ? 1 : 20), sm ? 20 : 299);
+                const Real wgt = r - Real(d);
+                const typename P::Real2 t0 = P::ld2_any(rain_tab + 2 * (d - 1)), t1 = P::ld2_any(rain_tab + 2 * d);
+                vq = (t0.x + wgt * (t1.x - t0.x)) * fac[j];
+                vn = (t0.y + wgt * (t1.y - t0.y)) * fac[j];
+              } else {
+                typename P::Loc3 t3;
+                P::lookup3_from_dum1(mu_r, (mu_r + 1) * c, t3);
+                vq = P::apply_table3(a.tb.vm, t3) * fac[j];
+                vn = P::apply_table3(a.tb.vn, t3) * fac[j];
+              }
               n[j] = nr_i * cf[j];
             }
           } else {
@@ -407,6 +526,7 @@ struct Sediment {
             if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / P3_LDG(g_cfl + k), qi_i, ni_i, qm_i, bm_i);
             else { qi_i = q[j] / cf[j]; ni_i = n[j] / cf[j]; qm_i = qm[j] / cf[j]; bm_i = bm[j] / cf[j]; }   // exact: rho_rime = qm/bm is ill-conditioned
             if (qi_i > qsmall) {
+              if (fac[j] < 0) fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54));
               ni_i = P::rmax(ni_i, C::NSMALL);
               const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
               qm[j] = qm_i * cf[j];
@@ -488,6 +608,15 @@ struct PhaseC {
   using C = Cst<Real>;
   static P3_HD Real sp(double x) { return static_cast<Real>(x); }
   template <class T> static P3_HD void put(T* p, T v_new, T v_old) { if (!(v_new == v_old)) *p = v_new; }
+
+  // a column that left p3_main after part1 or part2 (p3_main_impl.hpp:237,258) keeps the part3 defaults of
+  // p3_main_init (p3_main_impl.hpp:40-47); this also overwrites the scratch value parked in diag_eff_radius_qc
+  static P3_HD void defaults(const MainArgs<Real>& a, int64_t col, int k) {
+    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = sp(10.e-6);
+    col_ptr(a, F_DIAG_EFF_RADIUS_QI, col)[k] = sp(25.e-6);
+    col_ptr(a, F_DIAG_EFF_RADIUS_QR, col)[k] = sp(500.e-6);
+    col_ptr(a, F_RHO_QI, col)[k] = 0;
+  }
 
   static P3_HD void level(const MainArgs<Real>& a, int64_t col, int k) {
     Real* const g_qc = col_ptr(a, F_QC, col) + k; Real* const g_nc = col_ptr(a, F_NC, col) + k;

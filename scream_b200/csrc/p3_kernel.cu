@@ -52,20 +52,124 @@ struct WarpDev {
   template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
 };
 
-constexpr int A_WARPS = 4;        // warps (columns) per CTA in phase A
-constexpr int B_WARPS = 4;        // warps per CTA in the sedimentation kernels
+constexpr int A_THREADS = 128;          // phase A: 4 warps per CTA
+constexpr int A_TILE_LEVELS = 4096;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
+constexpr int A_MAX_TILE_COLS = 128;
+constexpr int B_WARPS = 4;              // warps per CTA in the sedimentation kernels
 constexpr int C_THREADS = 256;
 
+struct AccShared {   // shared-memory accumulator of PhaseA::pass2_level
+  static __device__ __forceinline__ void or_(int* p, int v) { atomicOr(p, v); }
+  static __device__ __forceinline__ void min_(int* p, int v) { atomicMin(p, v); }
+  static __device__ __forceinline__ void max_(int* p, int v) { atomicMax(p, v); }
+};
+
+// Phase A for one tile of `tile_cols` consecutive columns (tile_cols * nk <= A_TILE_LEVELS).
+//   pass 1  thread per level, a warp reads 32 consecutive levels of a column: classify, finish the
+//           skip_all levels, append the others to the tile's list in shared memory (ballot-compacted);
+//   sort    counting sort of the list by key (species present, temperature regime), descending, so
+//           that the expensive classes start first and a warp's 32 lanes take the same branches of part2;
+//   pass 2  warps pull groups of 32 sorted entries from a shared counter and run part1+part2 on them;
+//   finish  one thread per column writes the column's flags and sedimentation ranges.
 template <typename Real, int MINB>
-__global__ void __launch_bounds__(A_WARPS * 32, MINB)
-p3_phase_a(const __grid_constant__ MainArgs<Real> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int warp = threadIdx.x >> 5;
-  Real* hist = reinterpret_cast<Real*>(smem_raw) + size_t(warp) * HIST_ROWS * a.nk;
-  const int64_t col = (int64_t)blockIdx.x * A_WARPS + warp;
-  if (col >= a.ncol) return;
-  WarpDev w;
-  PhaseA<Real, WarpDev>::run(w, a, col, hist);
+__global__ void __launch_bounds__(A_THREADS, MINB)
+p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
+  __shared__ unsigned short s_idx[A_TILE_LEVELS];      // pass-1 order: level index inside the tile
+  __shared__ unsigned char  s_key[A_TILE_LEVELS];
+  __shared__ unsigned short s_sorted[A_TILE_LEVELS];
+  __shared__ int s_acc[A_MAX_TILE_COLS][COL_ACC_N];
+  __shared__ int s_hist[A_NKEYS];
+  __shared__ int s_count, s_next;
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int nk = a.nk;
+  const int64_t col0 = (int64_t)blockIdx.x * tile_cols;
+  const int ncols = (int)((a.ncol - col0 < tile_cols) ? (a.ncol - col0) : tile_cols);
+  const int nlevels = ncols * nk;
+
+  for (int c = tid; c < ncols; c += A_THREADS) PhaseA<Real>::acc_init(s_acc[c]);
+  if (tid < A_NKEYS) s_hist[tid] = 0;
+  if (tid == 0) { s_count = 0; s_next = 0; }
+  __syncthreads();
+
+  // ---- pass 1 ---- two levels per thread and iteration: both sets of loads are in flight before either is consumed
+  for (int base = tid - lane; base < nlevels; base += 2 * A_THREADS) {
+    int idx[2], c[2], k[2], key[2] = {-1, -1};
+    typename PhaseA<Real>::In1 in[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      idx[u] = base + u * A_THREADS + lane;
+      c[u] = (int)(((unsigned)idx[u] * div_magic) >> 24);      // idx / nk for idx < 8192 (plan_launch checks the magic)
+      k[u] = idx[u] - c[u] * nk;
+      if (idx[u] < nlevels) PhaseA<Real>::pass1_load(a, col0 + c[u], k[u], in[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (idx[u] < nlevels) {
+        int fl = 0;
+        key[u] = PhaseA<Real>::pass1_level(a, col0 + c[u], k[u], in[u], fl);
+        if (fl) atomicOr(&s_acc[c[u]][CA_FLAGS], fl);
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, key[u] >= 0);
+      if (m) {
+        int pos = 0;
+        if (lane == 0) pos = atomicAdd(&s_count, __popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
+        if (key[u] >= 0) {
+          s_idx[pos] = (unsigned short)idx[u];
+          s_key[pos] = (unsigned char)key[u];
+          atomicAdd(&s_hist[key[u]], 1);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int count = s_count;
+
+  // ---- counting sort, descending key; s_hist becomes the running write offset of each key ----
+  if (tid < 32) {
+    const int n = s_hist[A_NKEYS - 1 - lane];     // lane 0 holds the largest key
+    int incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    s_hist[A_NKEYS - 1 - lane] = incl - n;
+  }
+  __syncthreads();
+  for (int base = tid - lane; base < count; base += A_THREADS) {
+    const int e = base + lane;
+    const int key = (e < count) ? (int)s_key[e] : -1;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (key >= 0) {
+      const int leader = __ffs(peers) - 1;
+      int pos = 0;
+      if (lane == leader) pos = atomicAdd(&s_hist[key], __popc(peers));
+      pos = __shfl_sync(peers, pos, leader) + __popc(peers & ((1u << lane) - 1u));
+      s_sorted[pos] = s_idx[e];
+    }
+  }
+  __syncthreads();
+
+  // ---- pass 2 ----
+  const int ngroups = (count + 31) >> 5;
+  for (;;) {
+    int g = 0;
+    if (lane == 0) g = atomicAdd(&s_next, 1);
+    g = __shfl_sync(0xffffffffu, g, 0);
+    if (g >= ngroups) break;
+    const int e = g * 32 + lane;
+    if (e < count) {
+      const int idx = s_sorted[e];
+      const int c = (int)(((unsigned)idx * div_magic) >> 24);
+      const int k = idx - c * nk;
+      const bool active = (s_acc[c][CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
+      PhaseA<Real>::template pass2_level<AccShared>(a, col0 + c, k, active, s_acc[c]);
+    }
+  }
+  __syncthreads();
+  for (int c = tid; c < ncols; c += A_THREADS) PhaseA<Real>::finish_column(a, col0 + c, s_acc[c]);
 }
 
 // Sedimentation of species SP for the columns whose window [k_qxtop, nk) needs exactly JW register slots
@@ -83,6 +187,17 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
   WarpDev w;
   const int lane = w.lane();
   constexpr int dbase = (SP == SP_CLOUD) ? D_QC_KTOP : (SP == SP_RAIN) ? D_QR_KTOP : D_QI_KTOP;
+  // rain: the (vm, vn) fall-speed slice of this run's mu_r column (4.8 KB in fp64) is staged in shared memory
+  __shared__ __align__(16) Real s_vmn[SP == SP_RAIN ? 2 * VT_D0 : 2];
+  const Real* rain_tab = nullptr;
+  if (SP == SP_RAIN) {
+    typename Phys<Real>::Loc3 tj;
+    Phys<Real>::lookup3_from_dum1(a.ro.constant_mu_rain, Real(0), tj);
+    const Real* src = a.tb.vmn + (size_t)(tj.dumjj - 1) * 2 * VT_D0;
+    for (int i = threadIdx.x; i < 2 * VT_D0; i += blockDim.x) s_vmn[i] = __ldg(src + i);
+    __syncthreads();
+    rain_tab = s_vmn;
+  }
   const unsigned nchunks = ((unsigned)a.ncol + chunk - 1) / chunk;
   for (;;) {
     unsigned c = 0;
@@ -102,7 +217,7 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
       todo &= todo - 1;
       const int kt = __shfl_sync(WarpDev::FULL, ktop, src);
       const int kb = __shfl_sync(WarpDev::FULL, kbot, src);
-      Sediment<Real, WarpDev, SP, JW>::run(w, a, c0 + src, kt, kb);
+      Sediment<Real, WarpDev, SP, JW>::run(w, a, c0 + src, kt, kb, rain_tab);
     }
   }
 }
@@ -116,7 +231,10 @@ p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   else col = idx / a.nk;
   if (col >= a.ncol) return;
   const int k = (int)(idx - col * a.nk);
-  if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) return;   // the column left p3_main before sedimentation
+  if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) {   // the column left p3_main before sedimentation
+    PhaseC<Real>::defaults(a, col, k);
+    return;
+  }
   PhaseC<Real>::level(a, col, k);
 }
 
@@ -154,8 +272,17 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return (int)e;
   if (nk < 1 || nk > MAX_NLEV) return (int)cudaErrorInvalidValue;
-  cfg->a_blocks = (ncol + A_WARPS - 1) / A_WARPS;
-  cfg->a_smem = A_WARPS * HIST_ROWS * nk * (int)sizeof(Real);
+  // phase A tiles: as many columns as the CTA's level list holds; small grids get smaller tiles so that
+  // every SM has work (4 resident CTAs per SM)
+  int tile = A_TILE_LEVELS / nk;
+  if (tile > A_MAX_TILE_COLS) tile = A_MAX_TILE_COLS;
+  while (tile > 4 && (long long)ncol < (long long)sms * 8 * tile) tile >>= 1;
+  if (tile < 1) tile = 1;
+  cfg->a_tile_cols = tile;
+  cfg->a_blocks = (ncol + tile - 1) / tile;
+  cfg->a_div_magic = ((1u << 24) + (unsigned)nk - 1u) / (unsigned)nk;   // idx / nk == (idx * magic) >> 24 for idx < A_TILE_LEVELS, nk <= 256
+  for (unsigned idx = 0; idx < (unsigned)(tile * nk); ++idx)
+    if (((idx * cfg->a_div_magic) >> 24) != idx / (unsigned)nk) return (int)cudaErrorInvalidValue;
   // chunk of the sedimentation work queues: as large as 32 columns (one per lane) when there is plenty of
   // work, smaller when the grid is small so that the slowest warp does not hold the tail
   int chunk = 32;
@@ -189,9 +316,9 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   mark(0);
   {
     static const int occ = [] { const char* e = getenv("P3B200_A_OCC"); return e ? atoi(e) : 4; }();
-    if (occ == 3) p3_phase_a<Real, 3><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
-    else if (occ == 4) p3_phase_a<Real, 4><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
-    else p3_phase_a<Real, 2><<<cfg.a_blocks, A_WARPS * 32, cfg.a_smem, stream>>>(a);
+    if (occ == 3) p3_phase_a<Real, 3><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    else if (occ == 4) p3_phase_a<Real, 4><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    else p3_phase_a<Real, 5><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
   }
   mark(1);
   // stream order cloud -> rain -> ice: precip_liq_surf is assigned by cloud and incremented by rain

@@ -10,7 +10,8 @@ namespace p3b200 {
 constexpr int NUM_SED_CLASSES = 4;   // register-window classes of the sedimentation launches: 1, 2, 4, 8 slots per lane
 
 struct LaunchConfig {
-  int a_blocks, a_smem;     // phase A: one warp per column, dynamic shared memory for the history rows
+  int a_blocks, a_tile_cols;   // phase A: one CTA per tile of a_tile_cols columns
+  unsigned a_div_magic;        // (idx * magic) >> 24 == idx / nk inside a tile
   int b_blocks[3][NUM_SED_CLASSES];   // sedimentation [cloud, rain, ice][JW = 1,2,4,8]: persistent grids (0 = class unused)
   int b_chunk;              // columns per work-queue grab (<= 32)
   int c_blocks;             // phase C: one thread per (column, level)

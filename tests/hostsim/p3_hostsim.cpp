@@ -26,7 +26,12 @@ template <typename Real>
 int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int ncol, int nlev, double dt,
         int predictNc, int prescribedCCN, int zero_flux_top, const P3B200Runtime* rt, int* diag) {
   using namespace p3b200;
-  std::vector<Real> ice(12000), coll(60000), vn(3000), vm(3000), revap(3000);
+  std::vector<Real> ice(12000), coll(60000), vn(3000), vm(3000), revap(3000), vmn(6000);
+  for (int j = 0; j < 10; ++j)
+    for (int i = 0; i < 300; ++i) {
+      vmn[size_t(j * 300 + i) * 2 + 0] = Real(t->vm_table_vals[i][j]);
+      vmn[size_t(j * 300 + i) * 2 + 1] = Real(t->vn_table_vals[i][j]);
+    }
   for (int i = 0; i < 12000; ++i) ice[i] = Real((&t->ice_table_vals[0][0][0][0])[i]);
   for (int i = 0; i < 60000; ++i) coll[i] = Real((&t->collect_table_vals[0][0][0][0][0])[i]);
   for (int i = 0; i < 3000; ++i) {
@@ -37,32 +42,38 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   for (int f = 0; f < F_NUM; ++f) { a.f[f] = static_cast<Real*>(fields[f]); a.stride[f] = strides[f]; }
   a.ncol = ncol; a.nk = nlev; a.dt = Real(dt); a.predictNc = predictNc; a.prescribedCCN = prescribedCCN;
   a.zero_flux_top = zero_flux_top;
-  a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data()};
+  a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data(), vmn.data()};
+  typename Phys<Real>::Loc3 tj;
+  Phys<Real>::lookup3_from_dum1(Real(rt ? rt->constant_mu_rain : 1.0), Real(0), tj);
+  const Real* rain_tab = vmn.data() + size_t(tj.dumjj - 1) * 600;
   P3B200Runtime r;
   if (rt) r = *rt; else runtime_defaults(r);
   a.ro = make_runtime<Real>(r);
   std::vector<int> own_diag;
   if (!diag) { own_diag.assign(size_t(ncol) * D_NUM, 0); diag = own_diag.data(); }
   a.diag = diag; a.queue = nullptr;
-  std::vector<Real> hist(size_t(HIST_ROWS) * nlev);
   WarpSim w;
   // the three phases in the order the kernels run them (p3_kernel.cu: launch_main)
-  for (int i = 0; i < ncol; ++i) PhaseA<Real, WarpSim>::run(w, a, i, hist.data());
+  for (int i = 0; i < ncol; ++i) PhaseA<Real>::run_column_host(a, i);
   for (int i = 0; i < ncol; ++i) {
     const int* d = diag + size_t(i) * D_NUM;
     if (d[D_QC_KTOP] >= 0) Sediment<Real, WarpSim, SP_CLOUD, p3b200::MAX_NLEV>::run(w, a, i, d[D_QC_KTOP], d[D_QC_KBOT]);
   }
   for (int i = 0; i < ncol; ++i) {
     const int* d = diag + size_t(i) * D_NUM;
-    if (d[D_QR_KTOP] >= 0) Sediment<Real, WarpSim, SP_RAIN, p3b200::MAX_NLEV>::run(w, a, i, d[D_QR_KTOP], d[D_QR_KBOT]);
+    if (d[D_QR_KTOP] >= 0) Sediment<Real, WarpSim, SP_RAIN, p3b200::MAX_NLEV>::run(w, a, i, d[D_QR_KTOP], d[D_QR_KBOT], rain_tab);
   }
   for (int i = 0; i < ncol; ++i) {
     const int* d = diag + size_t(i) * D_NUM;
     if (d[D_QI_KTOP] >= 0) Sediment<Real, WarpSim, SP_ICE, p3b200::MAX_NLEV>::run(w, a, i, d[D_QI_KTOP], d[D_QI_KBOT]);
   }
-  for (int i = 0; i < ncol; ++i)
-    if (diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1)
-      for (int k = 0; k < nlev; ++k) PhaseC<Real>::level(a, i, k);
+  for (int i = 0; i < ncol; ++i) {
+    const bool full = diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1;
+    for (int k = 0; k < nlev; ++k) {
+      if (full) PhaseC<Real>::level(a, i, k);
+      else PhaseC<Real>::defaults(a, i, k);
+    }
+  }
   return 0;
 }
 }  // namespace
