@@ -137,6 +137,20 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
             int ncol, cudaStream_t stream, int* diag, const EventPair* ev) {
   MainArgs<Real> a;
   for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<Real*>(f->ptr[i]); a.stride[i] = f->col_stride[i]; }
+  // common column stride of the 2-D fields (flux arrays apart): enables the one-multiply addressing of the level kernels
+  a.ustride = 0; a.ustride_flux = 0;
+  {
+    int64_t u = -1;
+    bool same = true;
+    for (int i = 0; i < F_PRECIP_LIQ_SURF; ++i) {
+      if (!f->ptr[i] || i == F_PRECIP_LIQ_FLUX || i == F_PRECIP_ICE_FLUX) continue;
+      if (u < 0) u = f->col_stride[i];
+      else if (u != f->col_stride[i]) same = false;
+    }
+    if (same && u > 0 && f->col_stride[F_PRECIP_LIQ_FLUX] == f->col_stride[F_PRECIP_ICE_FLUX]) {
+      a.ustride = u; a.ustride_flux = f->col_stride[F_PRECIP_LIQ_FLUX];
+    }
+  }
   a.ncol = ncol; a.nk = in->nlev; a.dt = Real(in->dt);
   a.predictNc = in->predictNc; a.prescribedCCN = in->prescribedCCN; a.zero_flux_top = in->zero_flux_top;
   if constexpr (sizeof(Real) == 8) a.tb = h->tbd; else a.tb = h->tbf;

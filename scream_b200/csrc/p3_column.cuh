@@ -63,6 +63,8 @@ template <typename Real>
 struct MainArgs {
   Real*   f[F_NUM];
   int64_t stride[F_NUM];
+  int64_t ustride;         // common column stride of every 2-D field except the two flux arrays (0: strides differ)
+  int64_t ustride_flux;    // common column stride of precip_liq_flux / precip_ice_flux
   int     ncol, nk;
   Real    dt;
   int     predictNc, prescribedCCN, zero_flux_top;
@@ -74,6 +76,20 @@ struct MainArgs {
 
 template <typename Real>
 P3_HD Real* col_ptr(const MainArgs<Real>& a, int f, int64_t col) { return a.f[f] + col * a.stride[f]; }
+
+// Column addressing of the per-level kernels.  UNI = all 2-D fields share one column stride (what EAMxx and the
+// test bridge hand over unless a field is a sub-view of a bundled tracer array): one 64-bit multiply per level
+// instead of one per field (address arithmetic was ~13% of the instructions of the first kernels).
+template <bool UNI, typename Real>
+struct ColAddr {
+  int64_t col, off, off_flux;
+  P3_HD ColAddr(const MainArgs<Real>& a, int64_t c)
+      : col(c), off(UNI ? c * a.ustride : 0), off_flux(UNI ? c * a.ustride_flux : 0) {}
+  template <int F> P3_HD Real* p(const MainArgs<Real>& a) const {
+    if (UNI) return a.f[F] + ((F == F_PRECIP_LIQ_FLUX || F == F_PRECIP_ICE_FLUX) ? off_flux : off);
+    return a.f[F] + col * a.stride[F];
+  }
+};
 
 // =================================================================================================
 // Phase A: p3_main_init (p3_main_impl.hpp:21-72) + p3_main_part1 (p3_main_impl_part1.hpp:21-185) +
@@ -116,11 +132,13 @@ struct PhaseA {
 
   // ---- pass 1 -----------------------------------------------------------------------------------
   struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres; };
+  template <bool UNI>
   static P3_HD void pass1_load(const MainArgs<Real>& a, int64_t col, int k, In1& in) {
-    in.qc = col_ptr(a, F_QC, col)[k]; in.qr = col_ptr(a, F_QR, col)[k]; in.qi = col_ptr(a, F_QI, col)[k];
-    in.qv = col_ptr(a, F_QV, col)[k]; in.th = col_ptr(a, F_TH, col)[k];
-    in.inv_exner = P3_LDG(col_ptr(a, F_INV_EXNER, col) + k);
-    in.pres = P3_LDG(col_ptr(a, F_PRES, col) + k);
+    const ColAddr<UNI, Real> cp(a, col);
+    in.qc = cp.template p<F_QC>(a)[k]; in.qr = cp.template p<F_QR>(a)[k]; in.qi = cp.template p<F_QI>(a)[k];
+    in.qv = cp.template p<F_QV>(a)[k]; in.th = cp.template p<F_TH>(a)[k];
+    in.inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
+    in.pres = P3_LDG(cp.template p<F_PRES>(a) + k);
   }
 
   // Single-precision estimate of qv / qv_sat_i(T0, pres) on a cold level (relative error < 1e-4: fp32
@@ -151,7 +169,9 @@ struct PhaseA {
 
   // Returns -1 when the level is finished (skip_all; state stored), else its sort key in [0, A_NKEYS).
   // `flags` receives CF_NUC / CF_HYD1 / error bits of this level (to be OR-ed into the column's accumulator).
+  template <bool UNI>
   static P3_HD int pass1_level(const MainArgs<Real>& a, int64_t col, int k, const In1& in, int& flags) {
+    const ColAddr<UNI, Real> cp(a, col);
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
     Real qc = in.qc, qr = in.qr, qi = in.qi, qv = in.qv, th = in.th;
     const Real inv_exner = in.inv_exner;
@@ -203,35 +223,36 @@ struct PhaseA {
     }
     // the level is complete: every hydrometeor was clipped into vapour (p3_main_impl_part1.hpp:123-175),
     // part2 does not run (p3_main_impl.hpp:211-217: its outputs stay zero)
-    col_ptr(a, F_QC, col)[k] = 0; col_ptr(a, F_NC, col)[k] = 0; col_ptr(a, F_QR, col)[k] = 0; col_ptr(a, F_NR, col)[k] = 0;
-    col_ptr(a, F_QI, col)[k] = 0; col_ptr(a, F_QM, col)[k] = 0; col_ptr(a, F_NI, col)[k] = 0; col_ptr(a, F_BM, col)[k] = 0;
-    col_ptr(a, F_QV, col)[k] = qv; col_ptr(a, F_TH, col)[k] = th;
-    col_ptr(a, F_QV2QI_DEPOS_TEND, col)[k] = 0; col_ptr(a, F_PRECIP_TOTAL_TEND, col)[k] = 0; col_ptr(a, F_NEVAPR, col)[k] = 0;
-    col_ptr(a, F_PRECIP_LIQ_FLUX, col)[k] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[k] = 0;
-    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = (T < C::T_homogfrz) ? -T0 : T0;
+    cp.template p<F_QC>(a)[k] = 0; cp.template p<F_NC>(a)[k] = 0; cp.template p<F_QR>(a)[k] = 0; cp.template p<F_NR>(a)[k] = 0;
+    cp.template p<F_QI>(a)[k] = 0; cp.template p<F_QM>(a)[k] = 0; cp.template p<F_NI>(a)[k] = 0; cp.template p<F_BM>(a)[k] = 0;
+    cp.template p<F_QV>(a)[k] = qv; cp.template p<F_TH>(a)[k] = th;
+    cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = 0; cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = 0; cp.template p<F_NEVAPR>(a)[k] = 0;
+    cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
+    cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = (T < C::T_homogfrz) ? -T0 : T0;
     return -1;
   }
 
   // ---- pass 2 -----------------------------------------------------------------------------------
   // `col_active` = nucleationPossible || hydrometeorsPresent of the column (known after pass 1).
-  template <class AT>
+  template <class AT, bool UNI>
   static P3_HD void pass2_level(const MainArgs<Real>& a, int64_t col, int k, bool col_active, int* acc) {
+    const ColAddr<UNI, Real> cp(a, col);
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
     const Real dt = a.dt, inv_dt = 1 / a.dt;
     const bool predictNc = a.predictNc != 0, prescribedCCN = a.prescribedCCN != 0;
-    Real* const g_qc = col_ptr(a, F_QC, col) + k; Real* const g_nc = col_ptr(a, F_NC, col) + k;
-    Real* const g_qr = col_ptr(a, F_QR, col) + k; Real* const g_nr = col_ptr(a, F_NR, col) + k;
-    Real* const g_qi = col_ptr(a, F_QI, col) + k; Real* const g_qm = col_ptr(a, F_QM, col) + k;
-    Real* const g_ni = col_ptr(a, F_NI, col) + k; Real* const g_bm = col_ptr(a, F_BM, col) + k;
-    Real* const g_qv = col_ptr(a, F_QV, col) + k; Real* const g_th = col_ptr(a, F_TH, col) + k;
+    Real* const g_qc = cp.template p<F_QC>(a) + k; Real* const g_nc = cp.template p<F_NC>(a) + k;
+    Real* const g_qr = cp.template p<F_QR>(a) + k; Real* const g_nr = cp.template p<F_NR>(a) + k;
+    Real* const g_qi = cp.template p<F_QI>(a) + k; Real* const g_qm = cp.template p<F_QM>(a) + k;
+    Real* const g_ni = cp.template p<F_NI>(a) + k; Real* const g_bm = cp.template p<F_BM>(a) + k;
+    Real* const g_qv = cp.template p<F_QV>(a) + k; Real* const g_th = cp.template p<F_TH>(a) + k;
 
     typename P::Level L;
     L.qc = *g_qc; L.nc = *g_nc; L.qr = *g_qr; L.nr = *g_nr; L.qi = *g_qi;
     L.qm = *g_qm; L.ni = *g_ni; L.bm = *g_bm; L.qv = *g_qv; L.th = *g_th;
-    L.pres = P3_LDG(col_ptr(a, F_PRES, col) + k); L.inv_exner = P3_LDG(col_ptr(a, F_INV_EXNER, col) + k);
-    L.cf_i = P3_LDG(col_ptr(a, F_CLD_FRAC_I, col) + k); L.cf_l = P3_LDG(col_ptr(a, F_CLD_FRAC_L, col) + k);
-    L.cf_r = P3_LDG(col_ptr(a, F_CLD_FRAC_R, col) + k);
-    const Real dz = P3_LDG(col_ptr(a, F_DZ, col) + k), dpres = P3_LDG(col_ptr(a, F_DPRES, col) + k);
+    L.pres = P3_LDG(cp.template p<F_PRES>(a) + k); L.inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
+    L.cf_i = P3_LDG(cp.template p<F_CLD_FRAC_I>(a) + k); L.cf_l = P3_LDG(cp.template p<F_CLD_FRAC_L>(a) + k);
+    L.cf_r = P3_LDG(cp.template p<F_CLD_FRAC_R>(a) + k);
+    const Real dz = P3_LDG(cp.template p<F_DZ>(a) + k), dpres = P3_LDG(cp.template p<F_DPRES>(a) + k);
     // p3_main_init: p3_main_impl.hpp:21-72
     L.inv_cf_i = 1 / L.cf_i; L.inv_cf_l = 1 / L.cf_l; L.inv_cf_r = 1 / L.cf_r;
     const Real exner = 1 / L.inv_exner;
@@ -253,8 +274,8 @@ struct PhaseA {
       L.th = L.th - L.inv_exner * L.qc * latvap * inv_cp;
       L.qc = 0; L.nc = 0;
     } else {
-      if (prescribedCCN)  L.nc = P::rmax(L.nc, a.ro.spa_ccn_to_nc_factor * P3_LDG(col_ptr(a, F_NCCN, col) + k) / L.inv_cf_l);
-      else if (predictNc) L.nc = P::rmax(L.nc + P3_LDG(col_ptr(a, F_NC_NUCEAT_TEND, col) + k) * dt, sp(0.0));
+      if (prescribedCCN)  L.nc = P::rmax(L.nc, a.ro.spa_ccn_to_nc_factor * P3_LDG(cp.template p<F_NCCN>(a) + k) / L.inv_cf_l);
+      else if (predictNc) L.nc = P::rmax(L.nc + P3_LDG(cp.template p<F_NC_NUCEAT_TEND>(a) + k) * dt, sp(0.0));
       else                L.nc = C::NCCNST * L.inv_rho;
     }
     if (L.qr < qsmall) {
@@ -278,9 +299,9 @@ struct PhaseA {
 
     // p3_main_part2 (this level is not skip_all: pass 1 decided that on the same values)
     typename P::Part2Out o;
-    const Real* const g_ni_act = a.f[F_NI_ACTIVATED] ? col_ptr(a, F_NI_ACTIVATED, col) + k : nullptr;
+    const Real* const g_ni_act = a.f[F_NI_ACTIVATED] ? cp.template p<F_NI_ACTIVATED>(a) + k : nullptr;
     const bool h = P::part2_level(L, a.tb, a.ro, dt, inv_dt, predictNc, prescribedCCN,
-                                  col_ptr(a, F_QV_PREV, col) + k, col_ptr(a, F_T_PREV, col) + k, g_ni_act, o, err);
+                                  cp.template p<F_QV_PREV>(a) + k, cp.template p<F_T_PREV>(a) + k, g_ni_act, o, err);
     int fl = (h ? CF_HYD2 : 0) | (err << CF_ERR_SHIFT);
     if (fl) AT::or_(acc + CA_FLAGS, fl);
     // find_top / find_bottom (p3_find_impl.hpp) of the sedimenting species on the post-part2 state
@@ -289,18 +310,18 @@ struct PhaseA {
     if (L.qi >= qsmall) { AT::min_(acc + CA_LO_I, k); AT::max_(acc + CA_HI_I, k); }
     *g_qc = L.qc; *g_nc = L.nc; *g_qr = L.qr; *g_nr = L.nr; *g_qi = L.qi;
     *g_qm = L.qm; *g_ni = L.ni; *g_bm = L.bm; *g_qv = L.qv; *g_th = L.th;
-    col_ptr(a, F_QV2QI_DEPOS_TEND, col)[k] = o.qv2qi_depos_tend;
-    col_ptr(a, F_PRECIP_TOTAL_TEND, col)[k] = o.precip_total_tend;
-    col_ptr(a, F_NEVAPR, col)[k] = o.nevapr;
-    col_ptr(a, F_PRECIP_LIQ_FLUX, col)[k] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[k] = 0;
-    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = frz ? -T0 : T0;
+    cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = o.qv2qi_depos_tend;
+    cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = o.precip_total_tend;
+    cp.template p<F_NEVAPR>(a)[k] = o.nevapr;
+    cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
+    cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = frz ? -T0 : T0;
     // history arrays are only touched where part2 ran (p3_main_impl_part2.hpp:468-470), and part2 only runs
     // for columns that can nucleate or hold hydrometeors after part1 (p3_main_impl.hpp:237); for any other
     // column all tendencies of this level are exactly zero and the prognostics above are unchanged
     if (col_active) {
-      col_ptr(a, F_LIQ_ICE_EXCHANGE, col)[k] = o.liq_ice_exchange;
-      col_ptr(a, F_VAP_LIQ_EXCHANGE, col)[k] = o.vap_liq_exchange;
-      col_ptr(a, F_VAP_ICE_EXCHANGE, col)[k] = o.vap_ice_exchange;
+      cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = o.liq_ice_exchange;
+      cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = o.vap_liq_exchange;
+      cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = o.vap_ice_exchange;
     }
   }
 
@@ -330,14 +351,14 @@ struct PhaseA {
     for (int k = 0; k < a.nk; ++k) {
       int fl = 0;
       In1 in;
-      pass1_load(a, col, k, in);
-      keys[k] = pass1_level(a, col, k, in, fl);
+      pass1_load<false>(a, col, k, in);
+      keys[k] = pass1_level<false>(a, col, k, in, fl);
       acc[CA_FLAGS] |= fl;
     }
     const bool active = (acc[CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
     for (int key = A_NKEYS - 1; key >= 0; --key)
       for (int k = 0; k < a.nk; ++k)
-        if (keys[k] == key) pass2_level<AccPlain>(a, col, k, active, acc);
+        if (keys[k] == key) pass2_level<AccPlain, false>(a, col, k, active, acc);
     finish_column(a, col, acc);
   }
 };
@@ -478,7 +499,7 @@ struct Sediment {
             else { qc_i = q[j] * icf[j]; nc_i = n[j] * icf[j]; }
             if (qc_i > qsmall) {
               Real mu_c, lamc, d0, d1;
-              P::cloud_dsd2(qc_i, nc_i, rho[j], mu_c, lamc, d0, d1, false);
+              P::template cloud_dsd2<true>(qc_i, nc_i, rho[j], mu_c, lamc, d0, d1, false);
               n[j] = nc_i * cf[j];
               const Real acn = fac[j];
               // bcn = 2: pow(lamc, bcn) = lamc*lamc exactly for IEEE pow with an integral exponent 2
@@ -495,7 +516,7 @@ struct Sediment {
             if (qr_i > qsmall) {
               // get_rain_dsd2 + compute_rain_fall_velocity (p3_dsd2_impl.hpp:76-127, p3_rain_sed_impl.hpp:17-34)
               const Real nr_lim = P::rmax(nr_i, C::NSMALL);
-              Real c = std::cbrt(qr_i * P::fast_rcp(mass_to_d3 * nr_lim));      // 1/lamr
+              Real c = P::cbrt_quot(qr_i, mass_to_d3 * nr_lim);                // 1/lamr
               nr_i = nr_lim;
               if (c > c_max) { nr_i = qr_i * nr_per_q_min; c = c_max; }         // lamr < lammin
               else if (c < c_min) { nr_i = qr_i * nr_per_q_max; c = c_min; }    // lamr > lammax
@@ -532,7 +553,7 @@ struct Sediment {
               qm[j] = qm_i * cf[j];
               bm[j] = bm_i * cf[j];
               typename P::IceLoc ti;
-              P::lookup_ice(qi_i, ni_i, qm_i, rhop, ti);
+              P::template lookup_ice<true>(qi_i, ni_i, qm_i, rhop, ti);
               Real tv_ni_fallspd, tv_qi_fallspd, tv_ni_lammax, tv_ni_lammin;
               P::apply_table_ice2(0, a.tb.ice, ti, tv_ni_fallspd, tv_qi_fallspd);
               P::apply_table_ice2(6, a.tb.ice, ti, tv_ni_lammax, tv_ni_lammin);
@@ -611,19 +632,23 @@ struct PhaseC {
 
   // a column that left p3_main after part1 or part2 (p3_main_impl.hpp:237,258) keeps the part3 defaults of
   // p3_main_init (p3_main_impl.hpp:40-47); this also overwrites the scratch value parked in diag_eff_radius_qc
+  template <bool UNI>
   static P3_HD void defaults(const MainArgs<Real>& a, int64_t col, int k) {
-    col_ptr(a, F_DIAG_EFF_RADIUS_QC, col)[k] = sp(10.e-6);
-    col_ptr(a, F_DIAG_EFF_RADIUS_QI, col)[k] = sp(25.e-6);
-    col_ptr(a, F_DIAG_EFF_RADIUS_QR, col)[k] = sp(500.e-6);
-    col_ptr(a, F_RHO_QI, col)[k] = 0;
+    const ColAddr<UNI, Real> cp(a, col);
+    cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = sp(10.e-6);
+    cp.template p<F_DIAG_EFF_RADIUS_QI>(a)[k] = sp(25.e-6);
+    cp.template p<F_DIAG_EFF_RADIUS_QR>(a)[k] = sp(500.e-6);
+    cp.template p<F_RHO_QI>(a)[k] = 0;
   }
 
+  template <bool UNI>
   static P3_HD void level(const MainArgs<Real>& a, int64_t col, int k) {
-    Real* const g_qc = col_ptr(a, F_QC, col) + k; Real* const g_nc = col_ptr(a, F_NC, col) + k;
-    Real* const g_qr = col_ptr(a, F_QR, col) + k; Real* const g_nr = col_ptr(a, F_NR, col) + k;
-    Real* const g_qi = col_ptr(a, F_QI, col) + k; Real* const g_qm = col_ptr(a, F_QM, col) + k;
-    Real* const g_ni = col_ptr(a, F_NI, col) + k; Real* const g_bm = col_ptr(a, F_BM, col) + k;
-    Real* const g_stash = col_ptr(a, F_DIAG_EFF_RADIUS_QC, col) + k;
+    const ColAddr<UNI, Real> cp(a, col);
+    Real* const g_qc = cp.template p<F_QC>(a) + k; Real* const g_nc = cp.template p<F_NC>(a) + k;
+    Real* const g_qr = cp.template p<F_QR>(a) + k; Real* const g_nr = cp.template p<F_NR>(a) + k;
+    Real* const g_qi = cp.template p<F_QI>(a) + k; Real* const g_qm = cp.template p<F_QM>(a) + k;
+    Real* const g_ni = cp.template p<F_NI>(a) + k; Real* const g_bm = cp.template p<F_BM>(a) + k;
+    Real* const g_stash = cp.template p<F_DIAG_EFF_RADIUS_QC>(a) + k;
     const Real qc0 = *g_qc, nc0 = *g_nc, qr0 = *g_qr, nr0 = *g_nr, qi0 = *g_qi, qm0 = *g_qm, ni0 = *g_ni, bm0 = *g_bm;
     typename P::Part3Out o;
     o.eff_radius_qc = sp(10.e-6); o.eff_radius_qi = sp(25.e-6); o.eff_radius_qr = sp(500.e-6); o.rho_qi = 0;
@@ -633,24 +658,24 @@ struct PhaseC {
       put(g_nc, Real(0), nc0); put(g_nr, Real(0), nr0); put(g_ni, Real(0), ni0);
       put(g_qm, Real(0), qm0); put(g_bm, Real(0), bm0);
     } else {
-      Real* const g_qv = col_ptr(a, F_QV, col) + k; Real* const g_th = col_ptr(a, F_TH, col) + k;
+      Real* const g_qv = cp.template p<F_QV>(a) + k; Real* const g_th = cp.template p<F_TH>(a) + k;
       const Real qv0 = *g_qv, th0 = *g_th;
       Real qc = qc0, nc = nc0, qr = qr0, nr = nr0, qi = qi0, qm = qm0, ni = ni0, bm = bm0, qv = qv0, th = th0;
       const bool frz = *g_stash < 0;
-      const Real inv_exner = P3_LDG(col_ptr(a, F_INV_EXNER, col) + k);
+      const Real inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
       if (a.ro.do_ice_production)
         P::homogeneous_freezing_level(frz, inv_exner, qc, nc, qr, nr, qi, ni, qm, bm, th);
       // rho and the cloud fractions are only consumed where the species exists
       Real rho = 1, cf_l = 1, cf_r = 1, cf_i = 1;
       if (qc >= C::QSMALL || qi >= C::QSMALL)
-        rho = P3_LDG(col_ptr(a, F_DPRES, col) + k) / P3_LDG(col_ptr(a, F_DZ, col) + k) / C::gravit;
-      if (qc >= C::QSMALL) cf_l = P3_LDG(col_ptr(a, F_CLD_FRAC_L, col) + k);
-      if (qr >= C::QSMALL) cf_r = P3_LDG(col_ptr(a, F_CLD_FRAC_R, col) + k);
-      if (qi >= C::QSMALL) cf_i = P3_LDG(col_ptr(a, F_CLD_FRAC_I, col) + k);
+        rho = P3_LDG(cp.template p<F_DPRES>(a) + k) / P3_LDG(cp.template p<F_DZ>(a) + k) / C::gravit;
+      if (qc >= C::QSMALL) cf_l = P3_LDG(cp.template p<F_CLD_FRAC_L>(a) + k);
+      if (qr >= C::QSMALL) cf_r = P3_LDG(cp.template p<F_CLD_FRAC_R>(a) + k);
+      if (qi >= C::QSMALL) cf_i = P3_LDG(cp.template p<F_CLD_FRAC_I>(a) + k);
       Real sub_qc, sub_qr;
       P::part3_level(qc, nc, qr, nr, qi, ni, qm, bm, qv, th, rho, 1 / rho, inv_exner, cf_l, cf_r, cf_i, a.tb, a.ro, o, sub_qc, sub_qr);
       if (sub_qc != 0 || sub_qr != 0) {   // vap_liq_exchange read-modify-write, p3_main_impl_part3.hpp:97,127
-        Real* const g_vle = col_ptr(a, F_VAP_LIQ_EXCHANGE, col) + k;
+        Real* const g_vle = cp.template p<F_VAP_LIQ_EXCHANGE>(a) + k;
         Real v = *g_vle;
         v = v - sub_qc;
         v = v - sub_qr;
@@ -660,9 +685,9 @@ struct PhaseC {
       put(g_qm, qm, qm0); put(g_ni, ni, ni0); put(g_bm, bm, bm0); put(g_qv, qv, qv0); put(g_th, th, th0);
     }
     *g_stash = o.eff_radius_qc;
-    col_ptr(a, F_DIAG_EFF_RADIUS_QI, col)[k] = o.eff_radius_qi;
-    col_ptr(a, F_DIAG_EFF_RADIUS_QR, col)[k] = o.eff_radius_qr;
-    col_ptr(a, F_RHO_QI, col)[k] = o.rho_qi;
+    cp.template p<F_DIAG_EFF_RADIUS_QI>(a)[k] = o.eff_radius_qi;
+    cp.template p<F_DIAG_EFF_RADIUS_QR>(a)[k] = o.eff_radius_qr;
+    cp.template p<F_RHO_QI>(a)[k] = o.rho_qi;
   }
 };
 

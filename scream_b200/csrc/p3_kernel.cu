@@ -71,7 +71,7 @@ struct AccShared {   // shared-memory accumulator of PhaseA::pass2_level
 //           that the expensive classes start first and a warp's 32 lanes take the same branches of part2;
 //   pass 2  warps pull groups of 32 sorted entries from a shared counter and run part1+part2 on them;
 //   finish  one thread per column writes the column's flags and sedimentation ranges.
-template <typename Real, int MINB>
+template <typename Real, int MINB, bool UNI>
 __global__ void __launch_bounds__(A_THREADS, MINB)
 p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
   __shared__ unsigned short s_idx[A_TILE_LEVELS];      // pass-1 order: level index inside the tile
@@ -101,13 +101,13 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
       idx[u] = base + u * A_THREADS + lane;
       c[u] = (int)(((unsigned)idx[u] * div_magic) >> 24);      // idx / nk for idx < 8192 (plan_launch checks the magic)
       k[u] = idx[u] - c[u] * nk;
-      if (idx[u] < nlevels) PhaseA<Real>::pass1_load(a, col0 + c[u], k[u], in[u]);
+      if (idx[u] < nlevels) PhaseA<Real>::template pass1_load<UNI>(a, col0 + c[u], k[u], in[u]);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       if (idx[u] < nlevels) {
         int fl = 0;
-        key[u] = PhaseA<Real>::pass1_level(a, col0 + c[u], k[u], in[u], fl);
+        key[u] = PhaseA<Real>::template pass1_level<UNI>(a, col0 + c[u], k[u], in[u], fl);
         if (fl) atomicOr(&s_acc[c[u]][CA_FLAGS], fl);
       }
       const unsigned m = __ballot_sync(0xffffffffu, key[u] >= 0);
@@ -165,7 +165,7 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
       const int c = (int)(((unsigned)idx * div_magic) >> 24);
       const int k = idx - c * nk;
       const bool active = (s_acc[c][CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
-      PhaseA<Real>::template pass2_level<AccShared>(a, col0 + c, k, active, s_acc[c]);
+      PhaseA<Real>::template pass2_level<AccShared, UNI>(a, col0 + c, k, active, s_acc[c]);
     }
   }
   __syncthreads();
@@ -222,7 +222,7 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
   }
 }
 
-template <typename Real>
+template <typename Real, bool UNI>
 __global__ void __launch_bounds__(C_THREADS, 4)
 p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   const int64_t idx = (int64_t)blockIdx.x * C_THREADS + threadIdx.x;
@@ -232,10 +232,10 @@ p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   if (col >= a.ncol) return;
   const int k = (int)(idx - col * a.nk);
   if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) {   // the column left p3_main before sedimentation
-    PhaseC<Real>::defaults(a, col, k);
+    PhaseC<Real>::template defaults<UNI>(a, col, k);
     return;
   }
-  PhaseC<Real>::level(a, col, k);
+  PhaseC<Real>::template level<UNI>(a, col, k);
 }
 
 template <typename Kernel>
@@ -315,10 +315,12 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
   mark(0);
   {
-    static const int occ = [] { const char* e = getenv("P3B200_A_OCC"); return e ? atoi(e) : 4; }();
-    if (occ == 3) p3_phase_a<Real, 3><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
-    else if (occ == 4) p3_phase_a<Real, 4><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
-    else p3_phase_a<Real, 5><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    static const int occ = [] { const char* e = getenv("P3B200_A_OCC"); return e ? atoi(e) : 3; }();
+    const bool uni = a.ustride != 0 && a.ustride_flux != 0;
+#define P3_LAUNCH_A(OCC, UNI) p3_phase_a<Real, OCC, UNI><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic)
+    if (occ == 4) { if (uni) P3_LAUNCH_A(4, true); else P3_LAUNCH_A(4, false); }
+    else { if (uni) P3_LAUNCH_A(3, true); else P3_LAUNCH_A(3, false); }
+#undef P3_LAUNCH_A
   }
   mark(1);
   // stream order cloud -> rain -> ice: precip_liq_surf is assigned by cloud and incremented by rain
@@ -328,7 +330,8 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   mark(3);
   launch_species<Real, SP_ICE>(a, cfg, stream);
   mark(4);
-  p3_phase_c<Real><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  if (a.ustride != 0 && a.ustride_flux != 0) p3_phase_c<Real, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  else p3_phase_c<Real, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
   mark(5);
   return (int)cudaGetLastError();
 }

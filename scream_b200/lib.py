@@ -13,7 +13,7 @@ import numpy as np
 from .fields import FIELDS, INTERFACE_FIELDS, NUM_DIAG, RUNTIME_DEFAULTS, SURFACE_1D
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libp3b200.so")
+LIB_PATH = os.environ.get("P3B200_LIB", os.path.join(PKG_DIR, "libp3b200.so"))   # override: development only
 TABLE_BLOB = os.path.join(PKG_DIR, "data", "p3_lookup_table_1.v4.1.1.f64")
 NUM_FIELDS = len(FIELDS)
 

@@ -41,7 +41,7 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   MainArgs<Real> a;
   for (int f = 0; f < F_NUM; ++f) { a.f[f] = static_cast<Real*>(fields[f]); a.stride[f] = strides[f]; }
   a.ncol = ncol; a.nk = nlev; a.dt = Real(dt); a.predictNc = predictNc; a.prescribedCCN = prescribedCCN;
-  a.zero_flux_top = zero_flux_top;
+  a.zero_flux_top = zero_flux_top; a.ustride = 0; a.ustride_flux = 0;
   a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data(), vmn.data()};
   typename Phys<Real>::Loc3 tj;
   Phys<Real>::lookup3_from_dum1(Real(rt ? rt->constant_mu_rain : 1.0), Real(0), tj);
@@ -70,8 +70,8 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   for (int i = 0; i < ncol; ++i) {
     const bool full = diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1;
     for (int k = 0; k < nlev; ++k) {
-      if (full) PhaseC<Real>::level(a, i, k);
-      else PhaseC<Real>::defaults(a, i, k);
+      if (full) PhaseC<Real>::template level<false>(a, i, k);
+      else PhaseC<Real>::template defaults<false>(a, i, k);
     }
   }
   return 0;
