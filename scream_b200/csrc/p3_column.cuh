@@ -492,6 +492,11 @@ struct Sediment {
         const int k = kw + lane + j * WS;
         Real vq = 0, vn = 0;
         if (JW > 1 && kw + j * WS > k_qxbot) { Vq[j] = 0; Vn[j] = 0; continue; }   // warp-uniform: the front has not reached this slot
+        if (SP == SP_ICE) {
+          // rhofaci for the whole slot the first time any of its levels holds ice (one pow per slot and column, not
+          // one per sub-step as the front advances level by level); all lanes of the warp take part in the vote
+          if (w.any(fac[j] < 0 && k <= k_qxbot && q[j] > 0)) { if (fac[j] < 0) fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54)); }
+        }
         if (k <= k_qxbot) {
           if (SP == SP_CLOUD) {
             Real qc_i, nc_i;
@@ -547,7 +552,6 @@ struct Sediment {
             if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / P3_LDG(g_cfl + k), qi_i, ni_i, qm_i, bm_i);
             else { qi_i = q[j] / cf[j]; ni_i = n[j] / cf[j]; qm_i = qm[j] / cf[j]; bm_i = bm[j] / cf[j]; }   // exact: rho_rime = qm/bm is ill-conditioned
             if (qi_i > qsmall) {
-              if (fac[j] < 0) fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54));
               ni_i = P::rmax(ni_i, C::NSMALL);
               const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
               qm[j] = qm_i * cf[j];

@@ -2,4 +2,3 @@ one() { python bench.py --no-e2e --no-cpu --steps 4 "$@" 2>&1 | python -c "impor
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 echo base-mixed; one
 echo base-random; one --ic random
-echo occ4 mixed; P3B200_A_OCC=4 one
