@@ -645,29 +645,6 @@ struct PhaseC {
     cp.template p<F_RHO_QI>(a)[k] = 0;
   }
 
-  // Streaming pass of the phase-C tile kernel.  A level without any hydrometeor mass is finished here (part3 only
-  // zeroes the number/rime fields of the absent species, p3_main_impl_part3.hpp:98-100,128-130,190-196,201, and
-  // leaves the default diagnostics); any other level gets a class key for the sorted pass: bit 2 ice, bit 1 rain,
-  // bit 0 cloud present AFTER homogeneous freezing.  Returns -1 when the level is finished.
-  template <bool UNI>
-  static P3_HD int classify(const MainArgs<Real>& a, int64_t col, int k) {
-    const ColAddr<UNI, Real> cp(a, col);
-    const Real qc0 = cp.template p<F_QC>(a)[k], qr0 = cp.template p<F_QR>(a)[k], qi0 = cp.template p<F_QI>(a)[k];
-    if (qc0 == 0 && qr0 == 0 && qi0 == 0) {
-      Real* const g_nc = cp.template p<F_NC>(a) + k; Real* const g_nr = cp.template p<F_NR>(a) + k;
-      Real* const g_ni = cp.template p<F_NI>(a) + k; Real* const g_qm = cp.template p<F_QM>(a) + k;
-      Real* const g_bm = cp.template p<F_BM>(a) + k;
-      put(g_nc, Real(0), *g_nc); put(g_nr, Real(0), *g_nr); put(g_ni, Real(0), *g_ni);
-      put(g_qm, Real(0), *g_qm); put(g_bm, Real(0), *g_bm);
-      defaults<UNI>(a, col, k);
-      return -1;
-    }
-    const bool frz = a.ro.do_ice_production && cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] < 0;
-    const bool c = qc0 >= C::QSMALL, r = qr0 >= C::QSMALL;
-    const bool i = qi0 >= C::QSMALL || (frz && (c || r));
-    return (int(i) << 2) | (int(r && !frz) << 1) | int(c && !frz);
-  }
-
   template <bool UNI>
   static P3_HD void level(const MainArgs<Real>& a, int64_t col, int k) {
     const ColAddr<UNI, Real> cp(a, col);

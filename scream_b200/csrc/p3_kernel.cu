@@ -222,83 +222,20 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
   }
 }
 
-// Phase C for one tile of columns, same shape as phase A: a streaming pass (thread per level) finishes the levels
-// without hydrometeors and the columns that left p3_main early, the remaining levels are sorted by species class
-// and run homogeneous freezing + part3 with the 32 lanes of a warp on the same table/size-distribution branches.
-constexpr int C_TILE_THREADS = 128;
 template <typename Real, bool UNI>
-__global__ void __launch_bounds__(C_TILE_THREADS, 6)
-p3_phase_c(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
-  __shared__ unsigned short s_idx[A_TILE_LEVELS];
-  __shared__ unsigned char  s_key[A_TILE_LEVELS];
-  __shared__ unsigned short s_sorted[A_TILE_LEVELS];
-  __shared__ int s_hist[8];
-  __shared__ int s_count, s_next;
-
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int nk = a.nk;
-  const int64_t col0 = (int64_t)blockIdx.x * tile_cols;
-  const int ncols = (int)((a.ncol - col0 < tile_cols) ? (a.ncol - col0) : tile_cols);
-  const int nlevels = ncols * nk;
-  if (tid < 8) s_hist[tid] = 0;
-  if (tid == 0) { s_count = 0; s_next = 0; }
-  __syncthreads();
-
-  for (int base = tid - lane; base < nlevels; base += C_TILE_THREADS) {
-    const int idx = base + lane;
-    int key = -1;
-    if (idx < nlevels) {
-      const int c = (int)(((unsigned)idx * div_magic) >> 24);
-      const int k = idx - c * nk;
-      if (__ldg(a.diag + (col0 + c) * D_NUM + D_HYDRO_PART2) != 1) PhaseC<Real>::template defaults<UNI>(a, col0 + c, k);
-      else key = PhaseC<Real>::template classify<UNI>(a, col0 + c, k);
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, key >= 0);
-    if (m) {
-      int pos = 0;
-      if (lane == 0) pos = atomicAdd(&s_count, __popc(m));
-      pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
-      if (key >= 0) {
-        s_idx[pos] = (unsigned short)idx;
-        s_key[pos] = (unsigned char)key;
-        atomicAdd(&s_hist[key], 1);
-      }
-    }
+__global__ void __launch_bounds__(C_THREADS, 4)
+p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
+  const int64_t idx = (int64_t)blockIdx.x * C_THREADS + threadIdx.x;
+  int64_t col;
+  if (idx < (int64_t(1) << 32)) col = (int64_t)((unsigned)idx / (unsigned)a.nk);   // 32-bit divide on the common sizes
+  else col = idx / a.nk;
+  if (col >= a.ncol) return;
+  const int k = (int)(idx - col * a.nk);
+  if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) {   // the column left p3_main before sedimentation
+    PhaseC<Real>::template defaults<UNI>(a, col, k);
+    return;
   }
-  __syncthreads();
-  const int count = s_count;
-  if (count == 0) return;
-  if (tid == 0) {     // 8 keys: serial exclusive scan, descending key
-    int run = 0;
-    for (int key = 7; key >= 0; --key) { const int n = s_hist[key]; s_hist[key] = run; run += n; }
-  }
-  __syncthreads();
-  for (int base = tid - lane; base < count; base += C_TILE_THREADS) {
-    const int e = base + lane;
-    const int key = (e < count) ? (int)s_key[e] : -1;
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (key >= 0) {
-      const int leader = __ffs(peers) - 1;
-      int pos = 0;
-      if (lane == leader) pos = atomicAdd(&s_hist[key], __popc(peers));
-      pos = __shfl_sync(peers, pos, leader) + __popc(peers & ((1u << lane) - 1u));
-      s_sorted[pos] = s_idx[e];
-    }
-  }
-  __syncthreads();
-  const int ngroups = (count + 31) >> 5;
-  for (;;) {
-    int g = 0;
-    if (lane == 0) g = atomicAdd(&s_next, 1);
-    g = __shfl_sync(0xffffffffu, g, 0);
-    if (g >= ngroups) break;
-    const int e = g * 32 + lane;
-    if (e < count) {
-      const int idx = s_sorted[e];
-      const int c = (int)(((unsigned)idx * div_magic) >> 24);
-      PhaseC<Real>::template level<UNI>(a, col0 + c, idx - c * nk);
-    }
-  }
+  PhaseC<Real>::template level<UNI>(a, col, k);
 }
 
 template <typename Kernel>
@@ -393,8 +330,8 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   mark(3);
   launch_species<Real, SP_ICE>(a, cfg, stream);
   mark(4);
-  if (a.ustride != 0 && a.ustride_flux != 0) p3_phase_c<Real, true><<<cfg.a_blocks, C_TILE_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
-  else p3_phase_c<Real, false><<<cfg.a_blocks, C_TILE_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+  if (a.ustride != 0 && a.ustride_flux != 0) p3_phase_c<Real, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  else p3_phase_c<Real, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
   mark(5);
   return (int)cudaGetLastError();
 }

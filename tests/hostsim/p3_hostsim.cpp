@@ -70,8 +70,8 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   for (int i = 0; i < ncol; ++i) {
     const bool full = diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1;
     for (int k = 0; k < nlev; ++k) {
-      if (!full) PhaseC<Real>::template defaults<false>(a, i, k);
-      else if (PhaseC<Real>::template classify<false>(a, i, k) >= 0) PhaseC<Real>::template level<false>(a, i, k);
+      if (full) PhaseC<Real>::template level<false>(a, i, k);
+      else PhaseC<Real>::template defaults<false>(a, i, k);
     }
   }
   return 0;
