@@ -437,21 +437,33 @@ struct Sediment {
     const int kw = k_qxtop;
     Real q[JW], n[JW], qm[JW], bm[JW], rho[JW], inv_rho[JW], inv_dz[JW], cf[JW], icf[JW], fac[JW], acc[JW];
     // fac: cloud: acn; rain: rhofacr; ice: rhofaci
+    // all loads of the window first (up to 7 per slot in flight), then the divisions: the setup of a tall window
+    // was one exposed DRAM latency per slot and field
+    Real dzw[JW], dpw[JW], t0w[JW], cflw[JW];   // cflw: ice only, the liquid cloud fraction of bm_incld (first sub-step)
+#pragma unroll
+    for (int j = 0; j < JW; ++j) {
+      const int k = kw + lane + j * WS;
+      const bool in = k < nk;
+      q[j] = in ? g_q[k] : Real(0); n[j] = in ? g_n[k] : Real(0);
+      if (SP == SP_ICE) { qm[j] = in ? g_qm[k] : Real(0); bm[j] = in ? g_bm[k] : Real(0); }
+      dzw[j] = in ? P3_LDG(g_dz + k) : Real(1);
+      dpw[j] = in ? P3_LDG(g_dpres + k) : Real(1);
+      cf[j] = in ? P3_LDG(g_cf + k) : Real(1);
+      if (SP == SP_RAIN) acc[j] = in ? g_plf[k + 1] : Real(0);
+      if (SP == SP_CLOUD) t0w[j] = in ? std::abs(g_stash[k]) : Real(1);
+      if (SP == SP_ICE) cflw[j] = in ? P3_LDG(g_cfl + k) : Real(1);
+    }
 #pragma unroll
     for (int j = 0; j < JW; ++j) {
       const int k = kw + lane + j * WS;
       if (k < nk) {
-        q[j] = g_q[k]; n[j] = g_n[k];
-        if (SP == SP_ICE) { qm[j] = g_qm[k]; bm[j] = g_bm[k]; }
-        const Real dz = P3_LDG(g_dz + k);
-        rho[j] = P3_LDG(g_dpres + k) / dz / C::gravit;   // p3_main_impl_part1.hpp:93
+        const Real dz = dzw[j];
+        rho[j] = dpw[j] / dz / C::gravit;                 // p3_main_impl_part1.hpp:93
         inv_rho[j] = 1 / rho[j];
         inv_dz[j] = 1 / dz;                               // p3_main_impl.hpp:57
-        cf[j] = P3_LDG(g_cf + k);
         icf[j] = 1 / cf[j];
-        if (SP == SP_RAIN) acc[j] = g_plf[k + 1];
         if (SP == SP_CLOUD) {   // acn = g*rhow/(18*mu_air(T_atm at init)), p3_main_impl_part1.hpp:108-109
-          const Real T0 = std::abs(g_stash[k]);
+          const Real T0 = t0w[j];
           const Real dum = sp(1.496e-6) * P::pow1p5(T0) / (T0 + 120);
           fac[j] = C::gravit * C::RHO_H2O / (18 * dum);
         } else if (SP == SP_RAIN) {
@@ -460,9 +472,7 @@ struct Sediment {
           fac[j] = -1;    // rhofaci (p3_main_impl_part1.hpp:106) is evaluated when the level first holds ice
         }
       } else {
-        q[j] = 0; n[j] = 0; rho[j] = 1; inv_rho[j] = 1; inv_dz[j] = 0; cf[j] = 1; icf[j] = 1; fac[j] = 0;
-        if (SP == SP_ICE) { qm[j] = 0; bm[j] = 0; }
-        if (SP == SP_RAIN) acc[j] = 0;
+        rho[j] = 1; inv_rho[j] = 1; inv_dz[j] = 0; icf[j] = 1; fac[j] = 0;
       }
     }
 
@@ -509,10 +519,16 @@ struct Sediment {
               const Real acn = fac[j];
               // bcn = 2: pow(lamc, bcn) = lamc*lamc exactly for IEEE pow with an integral exponent 2
               const Real dum = 1 / (lamc * lamc);
-              // Gamma(4+bcn+mu)/Gamma(mu+4) = (mu+5)(mu+4), Gamma(1+bcn+mu)/Gamma(mu+1) = (mu+2)(mu+1):
-              // kept as tgamma quotients to follow the reference's rounding
+              // bcn = 2: Gamma(4+bcn+mu)/Gamma(mu+4) = (mu+5)(mu+4) and Gamma(1+bcn+mu)/Gamma(mu+1) = (mu+2)(mu+1)
+              // exactly; the products are within 1 ulp of the true quotient, closer than the quotient of two
+              // library tgamma values the reference forms (4 tgamma calls were 40 % of this kernel's instructions)
+#if defined(P3B200_EXACT_MATH)
               vq = acn * std::tgamma(4 + C::bcn + mu_c) * dum / std::tgamma(mu_c + 4);
               if (predictNc) vn = acn * std::tgamma(1 + C::bcn + mu_c) * dum / std::tgamma(mu_c + 1);
+#else
+              vq = acn * ((mu_c + 5) * (mu_c + 4)) * dum;
+              if (predictNc) vn = acn * ((mu_c + 2) * (mu_c + 1)) * dum;
+#endif
             }
           } else if (SP == SP_RAIN) {
             Real qr_i, nr_i;
@@ -549,7 +565,7 @@ struct Sediment {
             }
           } else {
             Real qi_i, ni_i, qm_i, bm_i;
-            if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / P3_LDG(g_cfl + k), qi_i, ni_i, qm_i, bm_i);
+            if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / cflw[j], qi_i, ni_i, qm_i, bm_i);
             else { qi_i = q[j] / cf[j]; ni_i = n[j] / cf[j]; qm_i = qm[j] / cf[j]; bm_i = bm[j] / cf[j]; }   // exact: rho_rime = qm/bm is ill-conditioned
             if (qi_i > qsmall) {
               ni_i = P::rmax(ni_i, C::NSMALL);
@@ -645,8 +661,10 @@ struct PhaseC {
     cp.template p<F_RHO_QI>(a)[k] = 0;
   }
 
+  // col_full: the column went through sedimentation (decided by the caller from the integer diagnostics; the
+  // kernel passes the value of a load that is still in flight, so that it overlaps the eight loads below)
   template <bool UNI>
-  static P3_HD void level(const MainArgs<Real>& a, int64_t col, int k) {
+  static P3_HD void level(const MainArgs<Real>& a, int64_t col, int k, bool col_full = true) {
     const ColAddr<UNI, Real> cp(a, col);
     Real* const g_qc = cp.template p<F_QC>(a) + k; Real* const g_nc = cp.template p<F_NC>(a) + k;
     Real* const g_qr = cp.template p<F_QR>(a) + k; Real* const g_nr = cp.template p<F_NR>(a) + k;
@@ -654,6 +672,7 @@ struct PhaseC {
     Real* const g_ni = cp.template p<F_NI>(a) + k; Real* const g_bm = cp.template p<F_BM>(a) + k;
     Real* const g_stash = cp.template p<F_DIAG_EFF_RADIUS_QC>(a) + k;
     const Real qc0 = *g_qc, nc0 = *g_nc, qr0 = *g_qr, nr0 = *g_nr, qi0 = *g_qi, qm0 = *g_qm, ni0 = *g_ni, bm0 = *g_bm;
+    if (!col_full) { defaults<UNI>(a, col, k); return; }
     typename P::Part3Out o;
     o.eff_radius_qc = sp(10.e-6); o.eff_radius_qi = sp(25.e-6); o.eff_radius_qr = sp(500.e-6); o.rho_qi = 0;
     if (qc0 == 0 && qr0 == 0 && qi0 == 0) {

@@ -231,11 +231,9 @@ p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   else col = idx / a.nk;
   if (col >= a.ncol) return;
   const int k = (int)(idx - col * a.nk);
-  if (__ldg(a.diag + col * D_NUM + D_HYDRO_PART2) != 1) {   // the column left p3_main before sedimentation
-    PhaseC<Real>::template defaults<UNI>(a, col, k);
-    return;
-  }
-  PhaseC<Real>::template level<UNI>(a, col, k);
+  // columns that left p3_main before sedimentation only get the part3 defaults
+  const int full = __ldg(a.diag + col * D_NUM + D_HYDRO_PART2);
+  PhaseC<Real>::template level<UNI>(a, col, k, full == 1);
 }
 
 template <typename Kernel>
