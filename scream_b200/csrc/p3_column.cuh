@@ -406,10 +406,10 @@ struct Sediment {
       Real up = w.shfl_up1(f);
       if (lane == 0) up = prev_last;
       if (JW > 1) prev_last = w.shfl_from(f, WS - 1);
-      if (in) {
-        const Real fluxdiv = (up - f) * inv_dz[j];
-        r[j] += fluxdiv * dt_sub * inv_rho[j];
-      }
+      // select instead of a branch (lanes outside the range compute a value nobody keeps)
+      const Real fluxdiv = (up - f) * inv_dz[j];
+      const Real r_new = r[j] + fluxdiv * dt_sub * inv_rho[j];
+      r[j] = in ? r_new : r[j];
       flux[j] = f;
     }
   }
@@ -493,6 +493,16 @@ struct Sediment {
     P::lookup3_from_dum1(mu_r, sp(0.0), tj);
     const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr && (tj.rdumjj - Real(tj.dumjj)) == 0;
 
+    // rain, fast-table path: the in-cloud values of the NEXT sub-step are carried in registers (what
+    // calculate_incloud_mixingratios left after part2 for the first one, q*(1/cld_frac) afterwards), and the
+    // fall-speed block is straight-line code on selects — in the first version 31 of the 256 instructions of a
+    // sub-step were BSSY/BRA/BSYNC and 33 were register moves of the branch joins
+    Real q_in[JW], n_in[JW];
+    if (SP == SP_RAIN) {
+#pragma unroll
+      for (int j = 0; j < JW; ++j) P::incloud_rain(q[j], n[j], icf[j], q_in[j], n_in[j]);
+    }
+
     while (dt_left > C::dt_left_tol) {
       const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
       Real Vq[JW], Vn[JW];
@@ -502,6 +512,34 @@ struct Sediment {
         const int k = kw + lane + j * WS;
         Real vq = 0, vn = 0;
         if (JW > 1 && kw + j * WS > k_qxbot) { Vq[j] = 0; Vn[j] = 0; continue; }   // warp-uniform: the front has not reached this slot
+        if (SP == SP_RAIN && rain_fast) {
+          const bool act = (k <= k_qxbot) && (q_in[j] > qsmall);
+          const Real qs = act ? q_in[j] : Real(1), ns = act ? n_in[j] : Real(1);
+          // get_rain_dsd2 + compute_rain_fall_velocity (p3_dsd2_impl.hpp:76-127, p3_rain_sed_impl.hpp:17-34)
+          const Real nr_lim = P::rmax(ns, C::NSMALL);
+          Real c = P::cbrt_quot(qs, mass_to_d3 * nr_lim);                  // 1/lamr
+          const bool lam_lo = c > c_max, lam_hi = c < c_min;               // lamr < lammin / lamr > lammax
+          const Real nr_i = lam_lo ? qs * nr_per_q_min : (lam_hi ? qs * nr_per_q_max : nr_lim);
+          c = lam_lo ? c_max : (lam_hi ? c_min : c);
+          // lookup (p3_table3_impl.hpp:17-65) with selects instead of the two-regime branch
+          const Real dum1 = (mu_r + 1) * c;
+          const bool sm = dum1 <= sp(195.e-6);
+          const Real x = dum1 * sp(1.e6);
+          Real r = sm ? (x + 5) * sp(0.1) : (x - 195) * (C::THIRD * sp(0.1)) + 20;
+          r = P::rmax(r, sm ? sp(1.0) : sp(20.0));
+          r = P::rmin(r, sm ? sp(20.0) : sp(300.0));
+          int d = static_cast<int>(r);
+          d = P::imin(P::imax(d, sm ? 1 : 20), sm ? 20 : 299);
+          const Real wgt = r - Real(d);
+          const typename P::Real2 t0 = P::ld2_any(rain_tab + 2 * (d - 1)), t1 = P::ld2_any(rain_tab + 2 * d);
+          vq = act ? (t0.x + wgt * (t1.x - t0.x)) * fac[j] : Real(0);
+          vn = act ? (t0.y + wgt * (t1.y - t0.y)) * fac[j] : Real(0);
+          n[j] = act ? nr_i * cf[j] : n[j];
+          const Real Co = vq * dt_left * inv_dz[j];
+          Co_loc = (Co > Co_loc) ? Co : Co_loc;
+          Vq[j] = vq; Vn[j] = vn;
+          continue;
+        }
         if (SP == SP_ICE) {
           // rhofaci for the whole slot the first time any of its levels holds ice (one pow per slot and column, not
           // one per sub-step as the front advances level by level); all lanes of the warp take part in the vote
@@ -531,9 +569,7 @@ struct Sediment {
 #endif
             }
           } else if (SP == SP_RAIN) {
-            Real qr_i, nr_i;
-            if (first) P::incloud_rain(q[j], n[j], icf[j], qr_i, nr_i);
-            else { qr_i = q[j] * icf[j]; nr_i = n[j] * icf[j]; }
+            Real qr_i = q_in[j], nr_i = n_in[j];
             if (qr_i > qsmall) {
               // get_rain_dsd2 + compute_rain_fall_velocity (p3_dsd2_impl.hpp:76-127, p3_rain_sed_impl.hpp:17-34)
               const Real nr_lim = P::rmax(nr_i, C::NSMALL);
@@ -604,9 +640,11 @@ struct Sediment {
 #pragma unroll
       for (int j = 0; j < JW; ++j) {
         const int k = kw + lane + j * WS;
-        if (k == kbot && k_qxbot == kbot) prt_local += flux[j] * dt_sub;
+        const Real prt_new = prt_local + flux[j] * dt_sub;
+        prt_local = (k == kbot && k_qxbot == kbot) ? prt_new : prt_local;
         // precip_liq_flux(k+1) += flux_qx(k) for k in [k_qxtop, new k_qxbot], p3_rain_sed_impl.hpp:139-153
-        if (SP == SP_RAIN && k <= k_temp) acc[j] = acc[j] + flux[j];
+        // (flux is exactly 0 outside that range and acc >= 0, so the add needs no guard)
+        if (SP == SP_RAIN) { acc[j] = acc[j] + flux[j]; q_in[j] = q[j] * icf[j]; n_in[j] = n[j] * icf[j]; }
       }
       if (k_qxbot != kbot) k_qxbot += 1;
       dt_left -= dt_sub;
