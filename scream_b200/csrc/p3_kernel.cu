@@ -52,8 +52,18 @@ struct WarpDev {
   template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
 };
 
-constexpr int A_THREADS = 128;          // phase A: 4 warps per CTA
-constexpr int A_TILE_LEVELS = 4096;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
+#if !defined(P3B200_A_THREADS)
+#define P3B200_A_THREADS 128
+#endif
+#if !defined(P3B200_A_TILE_LEVELS)
+#define P3B200_A_TILE_LEVELS 4096
+#endif
+#if !defined(P3B200_A_MINB)
+#define P3B200_A_MINB 3
+#endif
+constexpr int A_THREADS = P3B200_A_THREADS;
+constexpr int A_MIN_BLOCKS = P3B200_A_MINB;   // resident CTAs per SM the kernel is compiled for (register budget)          // phase A: 4 warps per CTA
+constexpr int A_TILE_LEVELS = P3B200_A_TILE_LEVELS;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
 constexpr int A_MAX_TILE_COLS = 128;
 constexpr int B_WARPS = 4;              // warps per CTA in the sedimentation kernels
 constexpr int C_THREADS = 256;
@@ -313,11 +323,9 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
   mark(0);
   {
-    static const int occ = [] { const char* e = getenv("P3B200_A_OCC"); return e ? atoi(e) : 3; }();
     const bool uni = a.ustride != 0 && a.ustride_flux != 0;
 #define P3_LAUNCH_A(OCC, UNI) p3_phase_a<Real, OCC, UNI><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic)
-    if (occ == 4) { if (uni) P3_LAUNCH_A(4, true); else P3_LAUNCH_A(4, false); }
-    else { if (uni) P3_LAUNCH_A(3, true); else P3_LAUNCH_A(3, false); }
+    if (uni) P3_LAUNCH_A(A_MIN_BLOCKS, true); else P3_LAUNCH_A(A_MIN_BLOCKS, false);
 #undef P3_LAUNCH_A
   }
   mark(1);
