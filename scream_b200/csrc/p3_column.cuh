@@ -489,9 +489,8 @@ struct Sediment {
     // the mu_r axis of the fall-speed tables (p3_table3_impl.hpp:52-62) is the same on every level: when its
     // interpolation weight is exactly 0 (integral mu_r) the bilinear form reduces bit for bit to the linear
     // interpolation along the size axis, read from the (vm, vn)-interleaved slice `rain_tab`
-    typename P::Loc3 tj;
-    P::lookup3_from_dum1(mu_r, sp(0.0), tj);
-    const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr && (tj.rdumjj - Real(tj.dumjj)) == 0;
+    // (the caller passes rain_tab only when that holds: p3_sediment checks the weight once per CTA)
+    const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr;
 
     // rain, fast-table path: the in-cloud values of the NEXT sub-step are carried in registers (what
     // calculate_incloud_mixingratios left after part2 for the first one, q*(1/cld_frac) afterwards), and the

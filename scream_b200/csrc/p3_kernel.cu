@@ -206,7 +206,7 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
     const Real* src = a.tb.vmn + (size_t)(tj.dumjj - 1) * 2 * VT_D0;
     for (int i = threadIdx.x; i < 2 * VT_D0; i += blockDim.x) s_vmn[i] = __ldg(src + i);
     __syncthreads();
-    rain_tab = s_vmn;
+    if (tj.rdumjj - Real(tj.dumjj) == 0) rain_tab = s_vmn;   // integral mu_r: the mu_r axis of the tables drops out
   }
   const unsigned nchunks = ((unsigned)a.ncol + chunk - 1) / chunk;
   for (;;) {

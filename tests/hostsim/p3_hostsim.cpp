@@ -45,7 +45,7 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data(), vmn.data()};
   typename Phys<Real>::Loc3 tj;
   Phys<Real>::lookup3_from_dum1(Real(rt ? rt->constant_mu_rain : 1.0), Real(0), tj);
-  const Real* rain_tab = vmn.data() + size_t(tj.dumjj - 1) * 600;
+  const Real* rain_tab = (tj.rdumjj - Real(tj.dumjj) == 0) ? vmn.data() + size_t(tj.dumjj - 1) * 600 : nullptr;
   P3B200Runtime r;
   if (rt) r = *rt; else runtime_defaults(r);
   a.ro = make_runtime<Real>(r);

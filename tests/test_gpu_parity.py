@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 from scream_b200 import ic_cases
-from scream_b200.fields import OUTPUTS
+from scream_b200.fields import OUTPUTS, PROGNOSTIC
 from tests import parity
 
 pytestmark = pytest.mark.gpu
@@ -134,3 +134,24 @@ def test_strided_tracer_views(oracle, handle64, p3lib):
     got = p3lib.to_host(dev)
     errs = parity.field_errors(ref, got)
     assert not _report(errs, parity.TOL[8]), _report(errs, parity.TOL[8])
+
+
+def test_runtime_knobs_generic_rain_table_path(oracle, handle64, p3lib):
+    """Non-default P3Runtime: a non-integral constant_mu_rain makes the mu_r axis of the rain tables matter
+    (bilinear path of p3_table3_impl.hpp:70-83 instead of the shared-memory slice), plus changed
+    autoconversion/accretion exponents and ice sedimentation factor."""
+    over = {"constant_mu_rain": 1.5, "autoconversion_qc_exponent": 2.3, "accretion_qr_exponent": 1.1,
+            "ice_sedimentation_factor": 0.9, "max_total_ni": 500.0e3}
+    f = ic_cases.make_mixed(3, 72)
+    ref = parity.clone(f)
+    parity.zero_outputs(ref)
+    _, d_ref = oracle.p3_main(ref, 300.0, True, True, runtime=over)
+    dev = p3lib.to_device(f)
+    for n in OUTPUTS:
+        if n not in PROGNOSTIC:
+            dev[n].zero_()
+    handle64.main(dev, 300.0, True, True, runtime=p3lib.make_runtime(over))
+    got = p3lib.to_host(dev)
+    errs = parity.field_errors(ref, got)
+    assert not _report(errs, parity.TOL[8]), _report(errs, parity.TOL[8])
+    assert np.array_equal(d_ref, handle64.get_diag(3))
