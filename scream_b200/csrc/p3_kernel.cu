@@ -66,7 +66,13 @@ constexpr int A_MIN_BLOCKS = P3B200_A_MINB;   // resident CTAs per SM the kernel
 constexpr int A_TILE_LEVELS = P3B200_A_TILE_LEVELS;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
 constexpr int A_MAX_TILE_COLS = 128;
 constexpr int B_WARPS = 4;              // warps per CTA in the sedimentation kernels
-constexpr int C_THREADS = 256;
+#if !defined(P3B200_C_THREADS)
+#define P3B200_C_THREADS 128
+#endif
+#if !defined(P3B200_C_MINB)
+#define P3B200_C_MINB 8
+#endif
+constexpr int C_THREADS = P3B200_C_THREADS;
 
 struct AccShared {   // shared-memory accumulator of PhaseA::pass2_level
   static __device__ __forceinline__ void or_(int* p, int v) { atomicOr(p, v); }
@@ -233,7 +239,7 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
 }
 
 template <typename Real, bool UNI>
-__global__ void __launch_bounds__(C_THREADS, 4)
+__global__ void __launch_bounds__(C_THREADS, P3B200_C_MINB)
 p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   const int64_t idx = (int64_t)blockIdx.x * C_THREADS + threadIdx.x;
   int64_t col;
