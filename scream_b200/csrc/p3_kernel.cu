@@ -194,11 +194,22 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
 // lowest 20-30 levels) run at 2-4x the occupancy of the tall ones.  Persistent warps grab chunks of
 // `chunk` (<= 32) consecutive columns from the launch's own atomic counter; lane i of the warp looks up
 // the range of column i of the chunk, a ballot selects the columns of this launch's class.
-constexpr int sed_min_blocks(int JW) { return JW == 1 ? 8 : JW == 2 ? 5 : JW == 4 ? 3 : 2; }
+// resident CTAs per SM each sedimentation instantiation is compiled for (its register budget), measured per
+// species: rain (JW=1) is issue-bound and likes 80 registers, ice on tall windows is latency-bound and is faster
+// with 16 warps/SM and a few spills than with 12 and none
+#if !defined(P3B200_B_RAIN1)
+#define P3B200_B_RAIN1 6
+#endif
+#if !defined(P3B200_B_ICE4)
+#define P3B200_B_ICE4 4
+#endif
+constexpr int sed_min_blocks(int SP, int JW) {
+  return JW == 1 ? (SP == SP_RAIN ? P3B200_B_RAIN1 : 8) : JW == 2 ? 5 : JW == 4 ? (SP == SP_ICE ? P3B200_B_ICE4 : 3) : 2;
+}
 __host__ __device__ constexpr int sed_class(int need) { return need <= 1 ? 1 : need <= 2 ? 2 : need <= 4 ? 4 : 8; }
 
 template <typename Real, int SP, int JW>
-__global__ void __launch_bounds__(B_WARPS * 32, sed_min_blocks(JW))
+__global__ void __launch_bounds__(B_WARPS * 32, sed_min_blocks(SP, JW))
 p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__ counter, const int chunk) {
   WarpDev w;
   const int lane = w.lane();
