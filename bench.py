@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target CPU work for the cpu_baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-prepost", action="store_true", help="skip the p3_preamble/p3_postamble bandwidth measurement")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     return ap.parse_args()
 
@@ -333,6 +334,39 @@ def run_b200(args):
                "d2h_bytes_per_step": d2h, "sample_columns_per_gpu": ecols, "ms_per_step": 1e3 * float(te.item()),
                "api": "p3b200_main_host (pinned host arrays, chunked H2D/kernel/D2H over 3 streams)"}
 
+    # ---- the brackets of P3Microphysics::run_impl around p3_main: two pure HBM streams ----
+    prepost = None
+    if not args.no_prepost:
+        try:
+            from scream_b200 import prepost_cases
+            from scream_b200.fields import PREAMBLE_ARRAYS_RW, POSTAMBLE_ARRAYS_RW
+            pcols = min(ncol, 524288)
+            t64 = prepost_cases.make_preamble(64, nlev, dtype)
+            pidx = torch.arange(pcols, device=dev) % 64
+            pre = {n: torch.from_numpy(v).to(dev).index_select(0, pidx).contiguous() for n, v in t64.items()}
+            p64 = prepost_cases.make_postamble(64, nlev, dtype)
+            post = {n: torch.from_numpy(v).to(dev).index_select(0, pidx).contiguous() for n, v in p64.items()}
+            res = {}
+            for name, fn, rw in (("preamble", lambda: handle.preamble(pre), PREAMBLE_ARRAYS_RW),
+                                 ("postamble", lambda: handle.postamble(post, dt), POSTAMBLE_ARRAYS_RW)):
+                for _ in range(3):
+                    fn()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(5):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / 5
+                gbs = sum(rw) * rb * pcols * nlev / (ms * 1e-3) / 1e9
+                res[name] = {"ms": ms, "columns": pcols, "arrays_read_written": list(rw), "achieved_gbs": gbs,
+                             "frac_of_hbm_peak": gbs / peak}
+            prepost = res
+            del pre, post
+        except Exception as exc:      # never let the side measurement take the headline down
+            prepost = {"error": repr(exc)}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_oracle_rate(args.ic, nlev, dt, rb, args.cpu_seconds, predict_nc, prescribed_ccn)
@@ -346,7 +380,7 @@ def run_b200(args):
                            "dt": dt, "columns_per_gpu": ncol, "flags": "predictNc=1,prescribedCCN=1",
                            "parallelism": f"columns block-sharded over {world} GPU(s), no collective in the step",
                            "l2": "inputs 72 GB >> 126 MB L2 and restored (16 GB written) between timed steps"},
-                "roofline": roofline, "conservation": budget, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "roofline": roofline, "run_impl_brackets": prepost, "conservation": budget, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": n_launch * args.steps, "column_error_bits": err_bits,
                 "step_ms": [round(x, 4) for x in step_ms],
                 "phase_ms_last_step": {k: round(v, 4) for k, v in phases.items()}}

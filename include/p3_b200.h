@@ -199,6 +199,42 @@ int p3b200_last_phase_ms(p3b200_handle h, double* ms5);
 int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
                                void* cuda_stream, double* totals4_dev, double* totals4_host);
 
+/* ---- P3Microphysics::run_impl brackets p3_main with p3_preamble / p3_postamble ------------------------
+ * (eamxx_p3_run.cpp:11-16, 39-44; functors eamxx_p3_process_interface.hpp:62-195, 200-262; the helper formulas
+ * are share/util/scream_common_physics_functions_impl.hpp:88-97, 115-118, 162-165, 214-222, 327-331, 375-379,
+ * 400-409).  Device pointers, (ncol, nlev) level-contiguous arrays that all share `col_stride`; the per-column
+ * arrays have ncol entries.  Both are one streaming pass, one thread per (column, level); in-place fields
+ * (wet <-> dry mixing ratios) are updated exactly where the reference updates them. */
+typedef struct P3B200PreambleFields {
+  /* in */
+  const void *pmid, *pseudo_density, *pseudo_density_dry, *T_atm, *cld_frac_t;
+  /* in/out: wet -> dry mixing ratio */
+  void *qv, *qc, *nc, *qr, *nr, *qi, *qm, *ni, *bm, *qv_prev;
+  /* out */
+  void *inv_exner, *th_atm, *cld_frac_l, *cld_frac_i, *cld_frac_r, *dz;
+  int64_t col_stride;
+} P3B200PreambleFields;
+int p3b200_preamble(p3b200_handle h, const P3B200PreambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream);
+
+typedef struct P3B200PostambleFields {
+  /* in */
+  const void *pmid, *pseudo_density, *pseudo_density_dry, *th_atm;
+  /* in/out */
+  void *T_atm;                                                   /* T before p3 in, rescaled new T out */
+  void *qv, *qc, *nc, *qr, *nr, *qi, *qm, *ni, *bm;              /* dry -> wet mixing ratio */
+  void *diag_eff_radius_qc, *diag_eff_radius_qi, *diag_eff_radius_qr;   /* m -> micron */
+  /* out */
+  void *T_prev, *qv_prev;
+  /* per column: fluxes from p3_main in, accumulated masses in/out, boundary fluxes out (all four NULL when
+   * compute_mass_and_energy_fluxes is off) */
+  const void *precip_liq_surf_flux, *precip_ice_surf_flux;
+  void *precip_liq_surf_mass, *precip_ice_surf_mass;
+  void *vapor_flux, *water_flux, *ice_flux, *heat_flux;
+  int64_t col_stride;
+  double dt;
+} P3B200PostambleFields;
+int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream);
+
 /* ---- the reference's own C bridge, re-implemented on the GPU ---------------------------------------
  * Drop-in for p3_main_f (p3_functions_f90.hpp:945-952; p3_functions_f90.cpp:1888-2103): HOST pointers,
  * Fortran (column-major) layout arr[i + ncol*k], 1-based its/kts (must be 1), outputs zeroed on entry.

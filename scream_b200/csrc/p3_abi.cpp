@@ -376,6 +376,35 @@ int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, cons
   return P3B200_OK;
 }
 
+int p3b200_preamble(p3b200_handle h, const P3B200PreambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream) {
+  if (!h || !f || ncol < 0 || nlev < 1 || f->col_stride < nlev) return P3B200_EINVAL;
+  const void* need[] = {f->pmid, f->pseudo_density, f->pseudo_density_dry, f->T_atm, f->cld_frac_t, f->qv, f->qc, f->nc,
+                        f->qr, f->nr, f->qi, f->qm, f->ni, f->bm, f->qv_prev, f->inv_exner, f->th_atm, f->cld_frac_l,
+                        f->cld_frac_i, f->cld_frac_r, f->dz};
+  for (const void* p : need) if (!p) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  const int rc = h->real_bytes == 8 ? preamble_from_abi<double>(f, ncol, nlev, cuda_stream)
+                                    : preamble_from_abi<float>(f, ncol, nlev, cuda_stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_preamble launch");
+  return P3B200_OK;
+}
+
+int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream) {
+  if (!h || !f || ncol < 0 || nlev < 1 || f->col_stride < nlev || !(f->dt > 0)) return P3B200_EINVAL;
+  const void* need[] = {f->pmid, f->pseudo_density, f->pseudo_density_dry, f->th_atm, f->T_atm, f->qv, f->qc, f->nc,
+                        f->qr, f->nr, f->qi, f->qm, f->ni, f->bm, f->diag_eff_radius_qc, f->diag_eff_radius_qi,
+                        f->diag_eff_radius_qr, f->T_prev, f->qv_prev, f->precip_liq_surf_flux, f->precip_ice_surf_flux,
+                        f->precip_liq_surf_mass, f->precip_ice_surf_mass};
+  for (const void* p : need) if (!p) return P3B200_EINVAL;
+  const int nflux = (f->vapor_flux != nullptr) + (f->water_flux != nullptr) + (f->ice_flux != nullptr) + (f->heat_flux != nullptr);
+  if (nflux != 0 && nflux != 4) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  const int rc = h->real_bytes == 8 ? postamble_from_abi<double>(f, ncol, nlev, cuda_stream)
+                                    : postamble_from_abi<float>(f, ncol, nlev, cuda_stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_postamble launch");
+  return P3B200_OK;
+}
+
 int p3b200_last_phase_ms(p3b200_handle h, double* ms5) {
   if (!h || !ms5) return P3B200_EINVAL;
   CU(cudaSetDevice(h->device));

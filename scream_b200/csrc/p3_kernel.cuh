@@ -35,4 +35,12 @@ template <typename Real>
 int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, int nparts, double* totals4, void* stream);
 
 }  // namespace p3b200
+
+// p3_prepost.cu: p3_preamble / p3_postamble launches from the C-ABI structs.  Return a cudaError_t as int.
+struct P3B200PreambleFields;
+struct P3B200PostambleFields;
+namespace p3b200 {
+template <typename Real> int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* stream);
+template <typename Real> int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream);
+}  // namespace p3b200
 #endif

@@ -1,0 +1,188 @@
+// p3_prepost.cu — p3_preamble / p3_postamble of P3Microphysics::run_impl as sm_100a kernels.
+//
+// Reference: the two functors of eamxx_p3_process_interface.hpp (p3_preamble :62-129, p3_postamble :200-262),
+// run once per column with a serial loop over the level packs (Kokkos RangePolicy over columns,
+// eamxx_p3_run.cpp:11-16, 39-44).  Here each is ONE streaming pass with one thread per (column, level):
+// consecutive threads own consecutive levels of a column, so every access is a coalesced row segment; the only
+// cross-level input (the max-overlap rain fraction needs cld_frac_t of the level above) is a second load of an
+// address the neighbouring lane fetches anyway.  Both kernels are pure HBM streams:
+//   preamble  15 reads + 16 writes per column-level (248 B in fp64)
+//   postamble 17 reads + 15 writes                  (256 B in fp64)
+// The helper formulas follow share/util/scream_common_physics_functions_impl.hpp (cited per line).
+#include "p3_kernel.cuh"
+#include "../../include/p3_b200.h"
+
+#include <cuda_runtime.h>
+
+namespace p3b200 {
+
+template <typename Real>
+struct PrePost {
+  using C = Cst<Real>;
+  // exner_function :88-97
+  static __device__ __forceinline__ Real exner(Real p) { return std::pow(p / C::P0, C::RD * C::INV_CP); }
+  // calculate_drymmr_from_wetmmr_dp_based :375-379 / calculate_wetmmr_from_drymmr_dp_based :327-331
+  static __device__ __forceinline__ Real dry(Real wet, Real pd, Real pdd) { return wet * pd / pdd; }
+  static __device__ __forceinline__ Real wet(Real dry, Real pd, Real pdd) { return dry * pdd / pd; }
+};
+
+template <typename Real>
+struct PreArgs {
+  const Real *pmid, *pd, *pdd, *T_atm, *cld_frac_t;
+  Real *q[10];                         // qv qc nc qr nr qi qm ni bm qv_prev
+  Real *inv_exner, *th_atm, *cld_frac_l, *cld_frac_i, *cld_frac_r, *dz;
+  int64_t stride;
+  int ncol, nk;
+};
+
+template <typename Real>
+__global__ void __launch_bounds__(256)
+p3_preamble_kernel(const __grid_constant__ PreArgs<Real> a) {
+  using PP = PrePost<Real>;
+  using C = Cst<Real>;
+  const int64_t total = (int64_t)a.ncol * a.nk;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int64_t col = idx / a.nk;
+    const int k = (int)(idx - col * a.nk);
+    const int64_t o = col * a.stride + k;
+    const Real pmid = __ldg(a.pmid + o), pd = __ldg(a.pd + o), pdd = __ldg(a.pdd + o), T = __ldg(a.T_atm + o);
+    const Real cft = __ldg(a.cld_frac_t + o);
+    const Real cft_up = (k != 0) ? __ldg(a.cld_frac_t + o - 1) : Real(0);
+    const Real qv_wet = a.q[0][o];
+    // calculate_dz :400-409 with calculate_virtual_temperature :214-222, on the WET qv (preamble l.78)
+    const Real c1 = -Real(1) + Real(1) / C::ep_2;
+    const Real T_virtual = T * (Real(1) + c1 * qv_wet);
+    a.dz[o] = (C::RD / C::gravit) * pd * T_virtual / pmid;
+    // wet -> dry (l.89-101)
+    a.q[0][o] = PP::dry(qv_wet, pd, pdd);
+#pragma unroll
+    for (int i = 1; i < 10; ++i) a.q[i][o] = PP::dry(a.q[i][o], pd, pdd);
+    // exner, theta (l.104-107; calculate_theta_from_T :115-118)
+    const Real ex = PP::exner(pmid);
+    a.inv_exner[o] = Real(1.0) / ex;
+    a.th_atm[o] = T / ex;
+    // cloud fractions (l.110-112) and max-overlap rain fraction (l.115-129)
+    const Real mincld = Real(0.0001);
+    const Real cf = cft < mincld ? mincld : cft;
+    a.cld_frac_l[o] = cf;
+    a.cld_frac_i[o] = cf;
+    a.cld_frac_r[o] = (k != 0 && cft_up > cf) ? cft_up : cf;
+  }
+}
+
+template <typename Real>
+struct PostArgs {
+  const Real *pmid, *pd, *pdd, *th_atm;
+  Real *T_atm, *T_prev, *qv_prev;
+  Real *q[9];                          // qc nc qr nr qi ni qm bm qv  (order of the reference, l.225-233)
+  Real *rad[3];
+  const Real *liq_flux, *ice_flux_in;
+  Real *liq_mass, *ice_mass, *vapor_flux, *water_flux, *ice_flux, *heat_flux;
+  int64_t stride;
+  int ncol, nk;
+  double dt;
+};
+
+template <typename Real>
+__global__ void __launch_bounds__(256)
+p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
+  using PP = PrePost<Real>;
+  using C = Cst<Real>;
+  const int64_t total = (int64_t)a.ncol * a.nk;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int64_t col = idx / a.nk;
+    const int k = (int)(idx - col * a.nk);
+    const int64_t o = col * a.stride + k;
+    const Real pmid = __ldg(a.pmid + o), pd = __ldg(a.pd + o), pdd = __ldg(a.pdd + o);
+    // temperature update with the dry/wet rescaling of dT (l.208-216; calculate_T_from_theta :162-165)
+    const Real T_before = a.T_atm[o];
+    Real T = (__ldg(a.th_atm + o) * PP::exner(pmid) - T_before) * pdd / pd;
+    T += T_before;
+    a.T_atm[o] = T;
+    a.T_prev[o] = T;
+    // dry -> wet (l.225-234)
+    Real qv_wet = 0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const Real v = PP::wet(a.q[i][o], pd, pdd);
+      a.q[i][o] = v;
+      if (i == 8) qv_wet = v;
+    }
+    a.qv_prev[o] = qv_wet;
+    // effective radii in microns (l.237-239)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) a.rad[i][o] *= Real(1e6);
+    if (k == 0) {
+      // accumulated surface masses and boundary fluxes (l.244-258); m_dt is a double in the reference
+      const Real lf = a.liq_flux[col], icf = a.ice_flux_in[col];
+      a.liq_mass[col] = Real(a.liq_mass[col] + lf * C::RHO_H2O * a.dt);
+      a.ice_mass[col] = Real(a.ice_mass[col] + icf * C::RHO_H2O * a.dt);
+      if (a.water_flux) {
+        a.vapor_flux[col] = 0;
+        a.water_flux[col] = lf + icf;
+        a.ice_flux[col] = icf;
+        a.heat_flux[col] = 0;
+      }
+    }
+  }
+}
+
+static int grid_for(long long total) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)sms * 8 * 4;      // a few waves of 8 resident CTAs per SM
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+template <typename Real>
+int launch_preamble(const PreArgs<Real>& a, void* stream) {
+  if (a.ncol <= 0) return 0;
+  p3_preamble_kernel<Real><<<grid_for((long long)a.ncol * a.nk), 256, 0, (cudaStream_t)stream>>>(a);
+  return (int)cudaGetLastError();
+}
+template <typename Real>
+int launch_postamble(const PostArgs<Real>& a, void* stream) {
+  if (a.ncol <= 0) return 0;
+  p3_postamble_kernel<Real><<<grid_for((long long)a.ncol * a.nk), 256, 0, (cudaStream_t)stream>>>(a);
+  return (int)cudaGetLastError();
+}
+
+// C-struct -> typed arguments (the C ABI structs hold void pointers)
+template <typename Real>
+int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* stream) {
+  PreArgs<Real> a;
+  a.pmid = (const Real*)f->pmid; a.pd = (const Real*)f->pseudo_density; a.pdd = (const Real*)f->pseudo_density_dry;
+  a.T_atm = (const Real*)f->T_atm; a.cld_frac_t = (const Real*)f->cld_frac_t;
+  void* q[10] = {f->qv, f->qc, f->nc, f->qr, f->nr, f->qi, f->qm, f->ni, f->bm, f->qv_prev};
+  for (int i = 0; i < 10; ++i) a.q[i] = (Real*)q[i];
+  a.inv_exner = (Real*)f->inv_exner; a.th_atm = (Real*)f->th_atm; a.cld_frac_l = (Real*)f->cld_frac_l;
+  a.cld_frac_i = (Real*)f->cld_frac_i; a.cld_frac_r = (Real*)f->cld_frac_r; a.dz = (Real*)f->dz;
+  a.stride = f->col_stride; a.ncol = ncol; a.nk = nlev;
+  return launch_preamble<Real>(a, stream);
+}
+template <typename Real>
+int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream) {
+  PostArgs<Real> a;
+  a.pmid = (const Real*)f->pmid; a.pd = (const Real*)f->pseudo_density; a.pdd = (const Real*)f->pseudo_density_dry;
+  a.th_atm = (const Real*)f->th_atm; a.T_atm = (Real*)f->T_atm; a.T_prev = (Real*)f->T_prev; a.qv_prev = (Real*)f->qv_prev;
+  void* q[9] = {f->qc, f->nc, f->qr, f->nr, f->qi, f->ni, f->qm, f->bm, f->qv};
+  for (int i = 0; i < 9; ++i) a.q[i] = (Real*)q[i];
+  a.rad[0] = (Real*)f->diag_eff_radius_qc; a.rad[1] = (Real*)f->diag_eff_radius_qi; a.rad[2] = (Real*)f->diag_eff_radius_qr;
+  a.liq_flux = (const Real*)f->precip_liq_surf_flux; a.ice_flux_in = (const Real*)f->precip_ice_surf_flux;
+  a.liq_mass = (Real*)f->precip_liq_surf_mass; a.ice_mass = (Real*)f->precip_ice_surf_mass;
+  a.vapor_flux = (Real*)f->vapor_flux; a.water_flux = (Real*)f->water_flux; a.ice_flux = (Real*)f->ice_flux;
+  a.heat_flux = (Real*)f->heat_flux;
+  a.stride = f->col_stride; a.ncol = ncol; a.nk = nlev; a.dt = f->dt;
+  return launch_postamble<Real>(a, stream);
+}
+
+template int preamble_from_abi<double>(const P3B200PreambleFields*, int, int, void*);
+template int preamble_from_abi<float>(const P3B200PreambleFields*, int, int, void*);
+template int postamble_from_abi<double>(const P3B200PostambleFields*, int, int, void*);
+template int postamble_from_abi<float>(const P3B200PostambleFields*, int, int, void*);
+
+}  // namespace p3b200

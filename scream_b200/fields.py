@@ -48,3 +48,21 @@ def algorithmic_bytes_per_col_level(real_bytes, predict_nc=True, prescribed_ccn=
     """SURVEY.md §8(d) / BASELINE.md §3: every live interface array touched once."""
     reads = 19 + (1 if prescribed_ccn else 0) + (2 if (predict_nc and not prescribed_ccn) else 0)
     return (reads + 22) * real_bytes
+
+
+# ---- P3Microphysics::run_impl brackets (eamxx_p3_process_interface.hpp:62-262) ------------------------------
+# Names in the order of the pointer tables of oracle/p3_oracle_prepost.cpp; the C ABI structs
+# (include/p3_b200.h: P3B200PreambleFields / P3B200PostambleFields) use the same member names.
+PREAMBLE_FIELDS = ("pmid", "pseudo_density", "pseudo_density_dry", "T_atm", "cld_frac_t",
+                   "qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm", "qv_prev",
+                   "inv_exner", "th_atm", "cld_frac_l", "cld_frac_i", "cld_frac_r", "dz")
+PREAMBLE_OUTPUTS = PREAMBLE_FIELDS[5:]
+POSTAMBLE_FIELDS_2D = ("pmid", "pseudo_density", "pseudo_density_dry", "th_atm", "T_atm",
+                       "qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm",
+                       "diag_eff_radius_qc", "diag_eff_radius_qi", "diag_eff_radius_qr", "T_prev", "qv_prev")
+POSTAMBLE_FIELDS_1D = ("precip_liq_surf_flux", "precip_ice_surf_flux", "precip_liq_surf_mass", "precip_ice_surf_mass",
+                       "vapor_flux", "water_flux", "ice_flux", "heat_flux")
+POSTAMBLE_OUTPUTS = POSTAMBLE_FIELDS_2D[4:] + POSTAMBLE_FIELDS_1D[2:]
+# compulsory HBM traffic per column-level (arrays read + written once), SURVEY.md §8(f) N1
+PREAMBLE_ARRAYS_RW = (15, 16)
+POSTAMBLE_ARRAYS_RW = (17, 15)

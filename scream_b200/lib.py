@@ -10,7 +10,8 @@ import subprocess
 
 import numpy as np
 
-from .fields import FIELDS, INTERFACE_FIELDS, NUM_DIAG, RUNTIME_DEFAULTS, SURFACE_1D
+from .fields import (FIELDS, INTERFACE_FIELDS, NUM_DIAG, POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D, PREAMBLE_FIELDS,
+                     RUNTIME_DEFAULTS, SURFACE_1D)
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("P3B200_LIB", os.path.join(PKG_DIR, "libp3b200.so"))   # override: development only
@@ -23,7 +24,7 @@ ABI_SYMBOLS = [
     "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
-    "p3b200_water_energy_totals", "p3b200_set_default_tables",
+    "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_p3_main_f",
 ]
 
@@ -128,6 +129,20 @@ def load_tables(blob=TABLE_BLOB, version=b"4.1.1"):
             return t
         _tables_cache = t
     return _tables_cache
+
+
+class P3B200PreambleFields(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in PREAMBLE_FIELDS] + [("col_stride", ctypes.c_int64)]
+
+
+class P3B200PostambleFields(ctypes.Structure):
+    # member order of include/p3_b200.h
+    _fields_ = [(n, ctypes.c_void_p) for n in
+                ("pmid", "pseudo_density", "pseudo_density_dry", "th_atm", "T_atm",
+                 "qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm",
+                 "diag_eff_radius_qc", "diag_eff_radius_qi", "diag_eff_radius_qr", "T_prev", "qv_prev",
+                 "precip_liq_surf_flux", "precip_ice_surf_flux", "precip_liq_surf_mass", "precip_ice_surf_mass",
+                 "vapor_flux", "water_flux", "ice_flux", "heat_flux")] + [("col_stride", ctypes.c_int64), ("dt", ctypes.c_double)]
 
 
 def make_runtime(overrides=None):
@@ -236,6 +251,31 @@ class P3Handle:
                                                ctypes.c_void_p(stream) if stream else None, None, out.ctypes.data),
               "p3b200_water_energy_totals")
         return out
+
+    def preamble(self, fields, stream=None):
+        """p3_preamble on device tensors (dict keyed by PREAMBLE_FIELDS, all (ncol, nlev) with one column stride)."""
+        f = P3B200PreambleFields()
+        ncol, nlev = fields["qv"].shape
+        for n in PREAMBLE_FIELDS:
+            t = fields[n]
+            assert t.is_cuda and t.stride(1) == 1 and t.stride(0) == fields["qv"].stride(0), n
+            setattr(f, n, t.data_ptr())
+        f.col_stride = fields["qv"].stride(0)
+        check(lib().p3b200_preamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_preamble")
+
+    def postamble(self, fields, dt, stream=None):
+        """p3_postamble on device tensors (POSTAMBLE_FIELDS_2D + POSTAMBLE_FIELDS_1D; the four boundary fluxes may be absent)."""
+        f = P3B200PostambleFields()
+        ncol, nlev = fields["qv"].shape
+        for n in POSTAMBLE_FIELDS_2D:
+            t = fields[n]
+            assert t.is_cuda and t.stride(1) == 1 and t.stride(0) == fields["qv"].stride(0), n
+            setattr(f, n, t.data_ptr())
+        for n in POSTAMBLE_FIELDS_1D:
+            setattr(f, n, fields[n].data_ptr() if n in fields and fields[n] is not None else None)
+        f.col_stride = fields["qv"].stride(0)
+        f.dt = float(dt)
+        check(lib().p3b200_postamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_postamble")
 
     def get_diag(self, ncol):
         out = np.empty((ncol, NUM_DIAG), dtype=np.int32)

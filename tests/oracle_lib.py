@@ -141,3 +141,36 @@ def set_math_scale(scale=None):
 
 def max_threads():
     return lib().p3o_max_threads()
+
+
+def _prepost_ptrs(fields, names, optional=()):
+    ptrs = (ctypes.c_void_p * len(names))()
+    for i, n in enumerate(names):
+        a = fields.get(n)
+        if a is None:
+            assert n in optional, n
+            ptrs[i] = None
+        else:
+            assert a.flags["C_CONTIGUOUS"], n
+            ptrs[i] = a.ctypes.data
+    return ptrs
+
+
+def preamble(fields):
+    """p3_preamble restatement (oracle/p3_oracle_prepost.cpp) in place on numpy arrays keyed by PREAMBLE_FIELDS."""
+    from scream_b200.fields import PREAMBLE_FIELDS
+    L = lib()
+    ncol, nlev = fields["qv"].shape
+    rc = L.p3o_preamble(fields["qv"].dtype.itemsize, _prepost_ptrs(fields, PREAMBLE_FIELDS), ncol, nlev)
+    assert rc == 0
+
+
+def postamble(fields, dt):
+    """p3_postamble restatement in place; the four boundary-flux arrays are optional."""
+    from scream_b200.fields import POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D
+    L = lib()
+    ncol, nlev = fields["qv"].shape
+    names = POSTAMBLE_FIELDS_2D + POSTAMBLE_FIELDS_1D
+    rc = L.p3o_postamble(fields["qv"].dtype.itemsize, _prepost_ptrs(fields, names, optional=POSTAMBLE_FIELDS_1D[4:]),
+                         ncol, nlev, ctypes.c_double(dt))
+    assert rc == 0
