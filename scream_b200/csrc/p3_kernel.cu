@@ -61,6 +61,10 @@ struct WarpDev {
 #if !defined(P3B200_A_MINB)
 #define P3B200_A_MINB 3
 #endif
+#if !defined(P3B200_A_P1_UNROLL)
+#define P3B200_A_P1_UNROLL 2
+#endif
+constexpr int A_P1_UNROLL = P3B200_A_P1_UNROLL;   // levels per thread in flight in the streaming pass
 constexpr int A_THREADS = P3B200_A_THREADS;
 constexpr int A_MIN_BLOCKS = P3B200_A_MINB;   // resident CTAs per SM the kernel is compiled for (register budget)          // phase A: 4 warps per CTA
 constexpr int A_TILE_LEVELS = P3B200_A_TILE_LEVELS;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
@@ -108,19 +112,20 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
   if (tid == 0) { s_count = 0; s_next = 0; }
   __syncthreads();
 
-  // ---- pass 1 ---- two levels per thread and iteration: both sets of loads are in flight before either is consumed
-  for (int base = tid - lane; base < nlevels; base += 2 * A_THREADS) {
-    int idx[2], c[2], k[2], key[2] = {-1, -1};
-    typename PhaseA<Real>::In1 in[2];
+  // ---- pass 1 ---- A_P1_UNROLL levels per thread and iteration: all their loads are in flight before any is consumed
+  for (int base = tid - lane; base < nlevels; base += A_P1_UNROLL * A_THREADS) {
+    int idx[A_P1_UNROLL], c[A_P1_UNROLL], k[A_P1_UNROLL], key[A_P1_UNROLL];
+    typename PhaseA<Real>::In1 in[A_P1_UNROLL];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < A_P1_UNROLL; ++u) {
+      key[u] = -1;
       idx[u] = base + u * A_THREADS + lane;
       c[u] = (int)(((unsigned)idx[u] * div_magic) >> 24);      // idx / nk for idx < 8192 (plan_launch checks the magic)
       k[u] = idx[u] - c[u] * nk;
       if (idx[u] < nlevels) PhaseA<Real>::template pass1_load<UNI>(a, col0 + c[u], k[u], in[u]);
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < A_P1_UNROLL; ++u) {
       if (idx[u] < nlevels) {
         int fl = 0;
         key[u] = PhaseA<Real>::template pass1_level<UNI>(a, col0 + c[u], k[u], in[u], fl);
