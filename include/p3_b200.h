@@ -36,6 +36,7 @@ extern "C" {
 #define P3B200_ENOMEM   -3   /* host or device allocation failed */
 #define P3B200_ETABLE   -4   /* lookup-table blob/text malformed or wrong version (p3_table_ice_impl.hpp:40-41) */
 #define P3B200_ECOLUMN  -5   /* a column raised a physics error flag (T<=0 / NaN / Co_max<0), see diag[P3B200_D_ERROR] */
+#define P3B200_EINTERNAL -6  /* two evaluations of the same property check disagree (fields modified concurrently?) */
 
 #define P3B200_MAX_NLEV 256  /* levels per column supported by the warp-per-column layout (8 per lane) */
 
@@ -234,6 +235,54 @@ typedef struct P3B200PostambleFields {
   double dt;
 } P3B200PostambleFields;
 int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream);
+
+/* ---- the property checks of the P3 process, as one fused reduction ---------------------------------
+ * P3Microphysics::initialize_impl registers 15 checks (eamxx_p3_process_interface.cpp:226-243): two invariant
+ * interval checks (T_mid, qv; qv repairable), eleven post-condition interval checks and two lower-bound checks.
+ * The atmosphere driver evaluates each one after run_impl as its own MinMaxLoc reduction over the field
+ * (share/property_checks/field_within_interval_check.cpp:80-226).  Here all 15 (min, max) pairs come out of ONE
+ * pass: either folded into the postamble (p3b200_postamble_checked — the values are in registers there, the
+ * checks cost no extra HBM traffic) or as a stand-alone pass over the 15 fields (p3b200_property_checks).
+ *
+ * out[i] follows the order of the add_*_check calls (P3B200_CHECK_* below).  `result` restates
+ * check_impl :202-226 with the bounds of :226-243: PASS when lb <= min and max <= ub; otherwise REPAIRABLE
+ * for a check registered with can_repair (only qv: its repairable bounds default to +-max), FAIL for the rest.
+ * min_loc/max_loc are flat (col * nlev + lev; col for the two per-column fields) indices of the LOWEST index holding
+ * the extreme value and are only computed when the check did not pass (-1 otherwise): the reference prints them
+ * only in its failure message, and the order in which Kokkos joins equal values is unspecified.  Values that are
+ * NaN are skipped, as the reference's `v < min` / `v > max` comparisons skip them.  Both calls synchronise the
+ * stream (the reference's reductions return to the host as well).
+ *
+ * p3b200_postamble_checked carries only a 30-bit violation mask through the postamble (bit 2i: some value of check
+ * i below lb, bit 2i+1: above ub — exactly "not Pass").  When the mask is zero all 15 results are PASS and
+ * min_val/max_val are NaN (the reference's Pass result carries no values either, check_impl :229-234); otherwise
+ * the call continues with the full reduction of p3b200_property_checks over the fields it has just written. */
+enum { P3B200_CHECK_T_MID = 0, P3B200_CHECK_QV, P3B200_CHECK_QC, P3B200_CHECK_QI, P3B200_CHECK_QR, P3B200_CHECK_QM,
+       P3B200_CHECK_NC, P3B200_CHECK_NR, P3B200_CHECK_NI, P3B200_CHECK_BM, P3B200_CHECK_PRECIP_LIQ_SURF_MASS,
+       P3B200_CHECK_PRECIP_ICE_SURF_MASS, P3B200_CHECK_EFF_RADIUS_QC, P3B200_CHECK_EFF_RADIUS_QI,
+       P3B200_CHECK_EFF_RADIUS_QR, P3B200_NUM_CHECKS };
+enum { P3B200_CHECK_PASS = 0, P3B200_CHECK_REPAIRABLE = 1, P3B200_CHECK_FAIL = 2 };
+typedef struct P3B200CheckResult {
+  double lb, ub;                 /* the registered bounds (ub = DBL_MAX for the lower-bound checks) */
+  double min_val, max_val;
+  int64_t min_loc, max_loc;
+  int32_t result;                /* P3B200_CHECK_PASS / _REPAIRABLE / _FAIL */
+  int32_t pass_lower, pass_upper;
+  int32_t reserved;
+} P3B200CheckResult;
+typedef struct P3B200CheckFields {
+  const void *T_mid, *qv, *qc, *qi, *qr, *qm, *nc, *nr, *ni, *bm;
+  const void *precip_liq_surf_mass, *precip_ice_surf_mass;      /* [ncol] */
+  const void *eff_radius_qc, *eff_radius_qi, *eff_radius_qr;    /* microns, as the postamble leaves them */
+  int64_t col_stride;
+} P3B200CheckFields;
+int p3b200_property_checks(p3b200_handle h, const P3B200CheckFields* f, int32_t ncol, int32_t nlev,
+                           P3B200CheckResult out[P3B200_NUM_CHECKS], void* cuda_stream);
+int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
+                             P3B200CheckResult out[P3B200_NUM_CHECKS], void* cuda_stream);
+/* FieldWithinIntervalCheck::repair_impl (field_within_interval_check.cpp:338-372) for the one repairable check:
+ * clip qv into its interval [1e-13, 0.2], in place. */
+int p3b200_repair_qv(p3b200_handle h, void* qv, int64_t col_stride, int32_t ncol, int32_t nlev, void* cuda_stream);
 
 /* ---- the reference's own C bridge, re-implemented on the GPU ---------------------------------------
  * Drop-in for p3_main_f (p3_functions_f90.hpp:945-952; p3_functions_f90.cpp:1888-2103): HOST pointers,

@@ -6,12 +6,15 @@
 // every compute entry point fails with P3B200_ECUDA when no CUDA device is usable.
 #include "p3_host.hpp"
 #include "p3_kernel.cuh"
+#include "p3_checks.cuh"
 
 #include <cuda_runtime.h>
 
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <cfloat>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -67,6 +70,7 @@ struct p3b200_ctx {
   Slot slots[NSLOT];
   LaunchConfig cfg{};
   int cfg_nk = -1, cfg_ncol = -1;
+  unsigned long long* d_checks = nullptr;   // 2*CHK_NUM min/max keys + 2 location slots (property checks)
   double* d_budget = nullptr;     // [budget_cols][4] per-column values + BUDGET_PARTS*4 partials + 4 totals
   size_t budget_cols = 0;
 };
@@ -191,6 +195,7 @@ const char* p3b200_strerror(int code) {
     case P3B200_ENOMEM: return "out of memory";
     case P3B200_ETABLE: return "lookup table malformed or wrong version";
     case P3B200_ECOLUMN: return "a column raised a physics error flag";
+    case P3B200_EINTERNAL: return "two evaluations of a property check disagree";
     default: return "unknown error";
   }
 }
@@ -256,6 +261,7 @@ int p3b200_destroy(p3b200_handle h) {
   if (h->d_diag) cudaFree(h->d_diag);
   if (h->d_queue) cudaFree(h->d_queue);
   if (h->d_budget) cudaFree(h->d_budget);
+  if (h->d_checks) cudaFree(h->d_checks);
   delete h;
   return P3B200_OK;
 }
@@ -389,7 +395,8 @@ int p3b200_preamble(p3b200_handle h, const P3B200PreambleFields* f, int32_t ncol
   return P3B200_OK;
 }
 
-int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream) {
+static int postamble_impl(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream,
+                          unsigned* check_mask) {
   if (!h || !f || ncol < 0 || nlev < 1 || f->col_stride < nlev || !(f->dt > 0)) return P3B200_EINVAL;
   const void* need[] = {f->pmid, f->pseudo_density, f->pseudo_density_dry, f->th_atm, f->T_atm, f->qv, f->qc, f->nc,
                         f->qr, f->nr, f->qi, f->qm, f->ni, f->bm, f->diag_eff_radius_qc, f->diag_eff_radius_qi,
@@ -399,9 +406,144 @@ int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t nc
   const int nflux = (f->vapor_flux != nullptr) + (f->water_flux != nullptr) + (f->ice_flux != nullptr) + (f->heat_flux != nullptr);
   if (nflux != 0 && nflux != 4) return P3B200_EINVAL;
   CU(cudaSetDevice(h->device));
-  const int rc = h->real_bytes == 8 ? postamble_from_abi<double>(f, ncol, nlev, cuda_stream)
-                                    : postamble_from_abi<float>(f, ncol, nlev, cuda_stream);
+  const int rc = h->real_bytes == 8 ? postamble_from_abi<double>(f, ncol, nlev, cuda_stream, check_mask)
+                                    : postamble_from_abi<float>(f, ncol, nlev, cuda_stream, check_mask);
   if (rc) return cuda_fail((cudaError_t)rc, "p3_postamble launch");
+  return P3B200_OK;
+}
+
+int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream) {
+  return postamble_impl(h, f, ncol, nlev, cuda_stream, nullptr);
+}
+
+// ---- property checks (eamxx_p3_process_interface.cpp:226-243) ----
+namespace {
+static_assert((int)CHK_NUM == (int)P3B200_NUM_CHECKS, "check tables out of step");
+struct CheckSpec { double lb, ub; bool can_repair; bool column_field; };
+inline CheckSpec check_spec(int i) { return {CHK_LB[i], CHK_UB[i], CHK_CAN_REPAIR[i], CHK_COLUMN_FIELD[i]}; }
+
+int checks_prepare(p3b200_handle h, cudaStream_t stream) {
+  if (!h->d_checks) CU(cudaMalloc(&h->d_checks, CHK_STATE_WORDS * sizeof(unsigned long long)));
+  const int rc = checks_reset(h->d_checks, h->real_bytes, stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_checks reset");
+  return P3B200_OK;
+}
+
+// check_impl :202-226 on the reduced (min, max), then the locations of the failing ones
+int checks_finish(p3b200_handle h, const void* const* field_ptrs, int64_t stride, int32_t ncol, int32_t nlev,
+                  P3B200CheckResult* out, cudaStream_t stream) {
+  unsigned long long keys[2 * P3B200_NUM_CHECKS];
+  CU(cudaMemcpyAsync(keys, h->d_checks, sizeof(keys), cudaMemcpyDeviceToHost, stream));
+  CU(cudaStreamSynchronize(stream));
+  const double s_max = std::numeric_limits<double>::max();
+  for (int i = 0; i < P3B200_NUM_CHECKS; ++i) {
+    const CheckSpec c = check_spec(i);
+    P3B200CheckResult& r = out[i];
+    r.lb = c.lb; r.ub = c.ub;
+    r.min_val = chk_decode(keys[2 * i]);
+    r.max_val = chk_decode(keys[2 * i + 1]);
+    r.min_loc = r.max_loc = -1;
+    r.pass_lower = r.pass_upper = 1;
+    r.reserved = 0;
+    const double lb_rep = c.can_repair ? -s_max : c.lb, ub_rep = c.can_repair ? s_max : c.ub;
+    if (r.min_val >= c.lb && r.max_val <= c.ub) {
+      r.result = P3B200_CHECK_PASS;
+      continue;
+    } else if (r.min_val < lb_rep || r.max_val > ub_rep) {
+      r.result = P3B200_CHECK_FAIL;
+      if (r.min_val < lb_rep) r.pass_lower = 0;
+      if (r.max_val > ub_rep) r.pass_upper = 0;
+    } else {
+      r.result = P3B200_CHECK_REPAIRABLE;
+      if (r.min_val < c.lb) r.pass_lower = 0;
+      if (r.max_val > c.ub) r.pass_upper = 0;
+    }
+    // locations (only printed by the reference when the check did not pass)
+    unsigned long long* loc_dev = h->d_checks + CHK_STATE_LOC;
+    CU(cudaMemsetAsync(loc_dev, 0xff, 2 * sizeof(unsigned long long), stream));
+    const int nk = c.column_field ? 1 : nlev;
+    const int64_t st = c.column_field ? 1 : stride;
+    for (int side = 0; side < 2; ++side) {
+      const double target = side ? r.max_val : r.min_val;
+      const int rc = h->real_bytes == 8 ? find_loc<double>(field_ptrs[i], st, ncol, nk, target, loc_dev + side, stream)
+                                        : find_loc<float>(field_ptrs[i], st, ncol, nk, target, loc_dev + side, stream);
+      if (rc) return cuda_fail((cudaError_t)rc, "p3_find_loc launch");
+    }
+    unsigned long long locs[2];
+    CU(cudaMemcpyAsync(locs, loc_dev, sizeof(locs), cudaMemcpyDeviceToHost, stream));
+    CU(cudaStreamSynchronize(stream));
+    r.min_loc = locs[0] == ~0ull ? -1 : (int64_t)locs[0];
+    r.max_loc = locs[1] == ~0ull ? -1 : (int64_t)locs[1];
+  }
+  return P3B200_OK;
+}
+}  // namespace
+
+static int property_checks_impl(p3b200_handle h, const P3B200CheckFields* f, int32_t ncol, int32_t nlev,
+                                P3B200CheckResult* out, void* cuda_stream) {
+  if (!h || !f || !out || ncol < 0 || nlev < 1 || f->col_stride < nlev) return P3B200_EINVAL;
+  const void* ptrs[P3B200_NUM_CHECKS] = {f->T_mid, f->qv, f->qc, f->qi, f->qr, f->qm, f->nc, f->nr, f->ni, f->bm,
+                                         f->precip_liq_surf_mass, f->precip_ice_surf_mass, f->eff_radius_qc,
+                                         f->eff_radius_qi, f->eff_radius_qr};
+  for (const void* p : ptrs) if (!p) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  int rc = checks_prepare(h, stream);
+  if (rc) return rc;
+  rc = h->real_bytes == 8 ? checks_from_abi<double>(f, ncol, nlev, cuda_stream, h->d_checks)
+                          : checks_from_abi<float>(f, ncol, nlev, cuda_stream, h->d_checks);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_checks launch");
+  return checks_finish(h, ptrs, f->col_stride, ncol, nlev, out, stream);
+}
+
+int p3b200_property_checks(p3b200_handle h, const P3B200CheckFields* f, int32_t ncol, int32_t nlev,
+                           P3B200CheckResult* out, void* cuda_stream) {
+  return property_checks_impl(h, f, ncol, nlev, out, cuda_stream);
+}
+
+int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
+                             P3B200CheckResult* out, void* cuda_stream) {
+  if (!h || !f || !out) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  if (!h->d_checks) CU(cudaMalloc(&h->d_checks, CHK_STATE_WORDS * sizeof(unsigned long long)));
+  unsigned* mask_dev = reinterpret_cast<unsigned*>(h->d_checks + CHK_STATE_MASK);
+  CU(cudaMemsetAsync(mask_dev, 0, sizeof(unsigned), stream));
+  const int rc = postamble_impl(h, f, ncol, nlev, cuda_stream, mask_dev);
+  if (rc) return rc;
+  unsigned mask = 0;
+  CU(cudaMemcpyAsync(&mask, mask_dev, sizeof(mask), cudaMemcpyDeviceToHost, stream));
+  CU(cudaStreamSynchronize(stream));
+  if (mask == 0) {
+    // every check passed: the reference's Pass result carries no extreme values (check_impl :229-234)
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    for (int i = 0; i < P3B200_NUM_CHECKS; ++i)
+      out[i] = P3B200CheckResult{CHK_LB[i], CHK_UB[i], nan, nan, -1, -1, P3B200_CHECK_PASS, 1, 1, 0};
+    return P3B200_OK;
+  }
+  // some check did not pass: the failure message needs extreme values and locations -> the full reduction over
+  // the fields the postamble has just written
+  P3B200CheckFields c;
+  c.T_mid = f->T_atm; c.qv = f->qv; c.qc = f->qc; c.qi = f->qi; c.qr = f->qr; c.qm = f->qm; c.nc = f->nc; c.nr = f->nr;
+  c.ni = f->ni; c.bm = f->bm; c.precip_liq_surf_mass = f->precip_liq_surf_mass;
+  c.precip_ice_surf_mass = f->precip_ice_surf_mass; c.eff_radius_qc = f->diag_eff_radius_qc;
+  c.eff_radius_qi = f->diag_eff_radius_qi; c.eff_radius_qr = f->diag_eff_radius_qr; c.col_stride = f->col_stride;
+  const int rc2 = property_checks_impl(h, &c, ncol, nlev, out, cuda_stream);
+  if (rc2) return rc2;
+  for (int i = 0; i < P3B200_NUM_CHECKS; ++i) {   // the two evaluations must agree on Pass / not-Pass
+    const bool flagged = (mask >> (2 * i)) & 3u;
+    if (flagged != (out[i].result != P3B200_CHECK_PASS)) return P3B200_EINTERNAL;
+  }
+  return P3B200_OK;
+}
+
+int p3b200_repair_qv(p3b200_handle h, void* qv, int64_t col_stride, int32_t ncol, int32_t nlev, void* cuda_stream) {
+  if (!h || !qv || ncol < 0 || nlev < 1 || col_stride < nlev) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  const CheckSpec c = check_spec(P3B200_CHECK_QV);
+  const int rc = h->real_bytes == 8 ? clip_field<double>(qv, col_stride, ncol, nlev, c.lb, c.ub, cuda_stream)
+                                    : clip_field<float>(qv, col_stride, ncol, nlev, c.lb, c.ub, cuda_stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_clip launch");
   return P3B200_OK;
 }
 

@@ -39,8 +39,17 @@ int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, i
 // p3_prepost.cu: p3_preamble / p3_postamble launches from the C-ABI structs.  Return a cudaError_t as int.
 struct P3B200PreambleFields;
 struct P3B200PostambleFields;
+struct P3B200CheckFields;
 namespace p3b200 {
 template <typename Real> int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* stream);
-template <typename Real> int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream);
+// check_mask: null, or the violation mask word (p3_checks.cuh) to fold the property checks into the pass
+template <typename Real> int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream,
+                                                unsigned* check_mask);
+int checks_reset(unsigned long long* state, int real_bytes, void* stream);
+template <typename Real> int checks_from_abi(const P3B200CheckFields* f, int ncol, int nlev, void* stream,
+                                             unsigned long long* state);
+template <typename Real> int find_loc(const void* field, int64_t stride, int ncol, int nk, double target,
+                                      unsigned long long* loc_dev, void* stream);
+template <typename Real> int clip_field(void* field, int64_t stride, int ncol, int nk, double lb, double ub, void* stream);
 }  // namespace p3b200
 #endif

@@ -1,4 +1,5 @@
-// p3_prepost.cu — p3_preamble / p3_postamble of P3Microphysics::run_impl as sm_100a kernels.
+// p3_prepost.cu — p3_preamble / p3_postamble of P3Microphysics::run_impl as sm_100a kernels, and the process's
+// property checks folded into the postamble pass (p3_checks.cuh).
 //
 // Reference: the two functors of eamxx_p3_process_interface.hpp (p3_preamble :62-129, p3_postamble :200-262),
 // run once per column with a serial loop over the level packs (Kokkos RangePolicy over columns,
@@ -10,6 +11,7 @@
 //   postamble 17 reads + 15 writes                  (256 B in fp64)
 // The helper formulas follow share/util/scream_common_physics_functions_impl.hpp (cited per line).
 #include "p3_kernel.cuh"
+#include "p3_checks.cuh"
 #include "../../include/p3_b200.h"
 
 #include <cuda_runtime.h>
@@ -81,13 +83,18 @@ struct PostArgs {
   int64_t stride;
   int ncol, nk;
   double dt;
+  unsigned* check_mask;                // CHECK only: the violation mask word (p3_checks.cuh)
 };
 
-template <typename Real>
+// CHECK folds the 15 property checks of initialize_impl (:226-243) into the pass: they are evaluated on the values
+// this kernel has just produced (what the reference's post-condition/invariant checks read from memory afterwards).
+template <typename Real, bool CHECK>
 __global__ void __launch_bounds__(256)
 p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
   using PP = PrePost<Real>;
   using C = Cst<Real>;
+  CheckFlags<Real> chk;
+  chk.init();
   const int64_t total = (int64_t)a.ncol * a.nk;
   for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
     const int64_t col = idx / a.nk;
@@ -100,23 +107,36 @@ p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
     T += T_before;
     a.T_atm[o] = T;
     a.T_prev[o] = T;
+    if (CHECK) chk.template see<CHK_T_MID>(T);
     // dry -> wet (l.225-234)
-    Real qv_wet = 0;
+    Real w[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) {
-      const Real v = PP::wet(a.q[i][o], pd, pdd);
-      a.q[i][o] = v;
-      if (i == 8) qv_wet = v;
+      w[i] = PP::wet(a.q[i][o], pd, pdd);
+      a.q[i][o] = w[i];
     }
-    a.qv_prev[o] = qv_wet;
+    a.qv_prev[o] = w[8];
     // effective radii in microns (l.237-239)
+    Real r[3];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) a.rad[i][o] *= Real(1e6);
+    for (int i = 0; i < 3; ++i) {
+      r[i] = a.rad[i][o] * Real(1e6);
+      a.rad[i][o] = r[i];
+    }
+    if (CHECK) {   // q[] order: qc nc qr nr qi ni qm bm qv
+      chk.template see<CHK_QC>(w[0]); chk.template see<CHK_NC>(w[1]); chk.template see<CHK_QR>(w[2]);
+      chk.template see<CHK_NR>(w[3]); chk.template see<CHK_QI>(w[4]); chk.template see<CHK_NI>(w[5]);
+      chk.template see<CHK_QM>(w[6]); chk.template see<CHK_BM>(w[7]); chk.template see<CHK_QV>(w[8]);
+      chk.template see<CHK_RAD_QC>(r[0]); chk.template see<CHK_RAD_QI>(r[1]); chk.template see<CHK_RAD_QR>(r[2]);
+    }
     if (k == 0) {
       // accumulated surface masses and boundary fluxes (l.244-258); m_dt is a double in the reference
       const Real lf = a.liq_flux[col], icf = a.ice_flux_in[col];
-      a.liq_mass[col] = Real(a.liq_mass[col] + lf * C::RHO_H2O * a.dt);
-      a.ice_mass[col] = Real(a.ice_mass[col] + icf * C::RHO_H2O * a.dt);
+      const Real lm = Real(a.liq_mass[col] + lf * C::RHO_H2O * a.dt);
+      const Real im = Real(a.ice_mass[col] + icf * C::RHO_H2O * a.dt);
+      a.liq_mass[col] = lm;
+      a.ice_mass[col] = im;
+      if (CHECK) { chk.template see<CHK_PRECIP_LIQ>(lm); chk.template see<CHK_PRECIP_ICE>(im); }
       if (a.water_flux) {
         a.vapor_flux[col] = 0;
         a.water_flux[col] = lf + icf;
@@ -124,6 +144,83 @@ p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
         a.heat_flux[col] = 0;
       }
     }
+  }
+  if (CHECK) chk.publish(a.check_mask);
+}
+
+// ---- the property checks on their own (for a caller that does not use the fused postamble) ----------------
+template <typename Real>
+struct CheckArgs {
+  const Real* f[CHK_NUM];              // CheckId order; CHK_PRECIP_* are per-column arrays
+  int64_t stride;
+  int ncol, nk;
+  unsigned long long* state;
+};
+
+// One launch for all 15 reductions: blockIdx.y picks the check, the blocks of a row stream that field with four
+// loads in flight per thread and keep ONE (min, max) pair.
+template <typename Real>
+__global__ void __launch_bounds__(256)
+p3_checks_kernel(const __grid_constant__ CheckArgs<Real> a) {
+  const int fid = blockIdx.y;
+  const bool column_field = fid == CHK_PRECIP_LIQ || fid == CHK_PRECIP_ICE;
+  const Real* __restrict__ f = a.f[fid];
+  const int nk = column_field ? 1 : a.nk;
+  const int64_t stride = column_field ? 1 : a.stride;
+  const int64_t total = (int64_t)a.ncol * nk;
+  const int64_t step = (int64_t)gridDim.x * 256;
+  const bool contiguous = stride == nk;
+  CheckMinMax<Real> mm;
+  mm.init();
+  for (int64_t base = (int64_t)blockIdx.x * 256 + threadIdx.x; base < total; base += 4 * step) {
+    Real v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t idx = base + j * step;
+      v[j] = CheckMinMax<Real>::skipped();
+      if (idx < total) {
+        const int64_t o = contiguous ? idx : (idx / nk) * stride + idx % nk;
+        v[j] = __ldg(f + o);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mm.see(v[j]);
+  }
+  mm.template publish<256>(a.state + 2 * fid);
+}
+
+// state[2i] = key(+big), state[2i+1] = key(-big): the Kokkos MinMaxLoc identities
+__global__ void p3_checks_reset_kernel(unsigned long long* state, double big) {
+  if (threadIdx.x < 2 * CHK_NUM) state[threadIdx.x] = chk_encode((threadIdx.x & 1) ? -big : big);
+}
+
+// Lowest flat index (col * nk + k, the reference's unflattened (col, lev) order) whose value equals `target`.
+// Only launched for a field whose check did not pass.
+template <typename Real>
+__global__ void __launch_bounds__(256)
+p3_find_loc_kernel(const Real* __restrict__ f, int64_t stride, int ncol, int nk, double target, unsigned long long* loc) {
+  const int64_t total = (int64_t)ncol * nk;
+  unsigned long long best = ~0ull;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int64_t col = idx / nk;
+    const int k = (int)(idx - col * nk);
+    if ((double)__ldg(f + col * stride + k) == target && (unsigned long long)idx < best) best = (unsigned long long)idx;
+  }
+  if (best != ~0ull) atomicMin(loc, best);
+}
+
+// FieldWithinIntervalCheck::repair_impl (field_within_interval_check.cpp:338-372): clip into [lb, ub]
+template <typename Real>
+__global__ void __launch_bounds__(256)
+p3_clip_kernel(Real* __restrict__ f, int64_t stride, int ncol, int nk, Real lb, Real ub) {
+  const int64_t total = (int64_t)ncol * nk;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int64_t col = idx / nk;
+    const int k = (int)(idx - col * nk);
+    Real v = f[col * stride + k];
+    v = ub < v ? ub : v;
+    v = lb > v ? lb : v;
+    f[col * stride + k] = v;
   }
 }
 
@@ -147,7 +244,9 @@ int launch_preamble(const PreArgs<Real>& a, void* stream) {
 template <typename Real>
 int launch_postamble(const PostArgs<Real>& a, void* stream) {
   if (a.ncol <= 0) return 0;
-  p3_postamble_kernel<Real><<<grid_for((long long)a.ncol * a.nk), 256, 0, (cudaStream_t)stream>>>(a);
+  const int grid = grid_for((long long)a.ncol * a.nk);
+  if (a.check_mask) p3_postamble_kernel<Real, true><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  else p3_postamble_kernel<Real, false><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   return (int)cudaGetLastError();
 }
 
@@ -165,8 +264,9 @@ int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* s
   return launch_preamble<Real>(a, stream);
 }
 template <typename Real>
-int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream) {
+int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream, unsigned* check_mask) {
   PostArgs<Real> a;
+  a.check_mask = check_mask;
   a.pmid = (const Real*)f->pmid; a.pd = (const Real*)f->pseudo_density; a.pdd = (const Real*)f->pseudo_density_dry;
   a.th_atm = (const Real*)f->th_atm; a.T_atm = (Real*)f->T_atm; a.T_prev = (Real*)f->T_prev; a.qv_prev = (Real*)f->qv_prev;
   void* q[9] = {f->qc, f->nc, f->qr, f->nr, f->qi, f->ni, f->qm, f->bm, f->qv};
@@ -180,9 +280,50 @@ int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void*
   return launch_postamble<Real>(a, stream);
 }
 
+int checks_reset(unsigned long long* state, int real_bytes, void* stream) {
+  p3_checks_reset_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(state, real_bytes == 8 ? DBL_MAX : (double)FLT_MAX);
+  return (int)cudaGetLastError();
+}
+
+template <typename Real>
+int checks_from_abi(const P3B200CheckFields* f, int ncol, int nlev, void* stream, unsigned long long* state) {
+  if (ncol <= 0) return 0;
+  CheckArgs<Real> a;
+  const void* src[CHK_NUM] = {f->T_mid, f->qv, f->qc, f->qi, f->qr, f->qm, f->nc, f->nr, f->ni, f->bm,
+                              f->precip_liq_surf_mass, f->precip_ice_surf_mass, f->eff_radius_qc, f->eff_radius_qi,
+                              f->eff_radius_qr};
+  for (int i = 0; i < CHK_NUM; ++i) a.f[i] = (const Real*)src[i];
+  a.stride = f->col_stride; a.ncol = ncol; a.nk = nlev; a.state = state;
+  int gx = grid_for(((long long)ncol * nlev + 3) / 4);
+  if (gx > 148 * 8) gx = 148 * 8;       // x CHK_NUM rows: a few waves of 8 resident CTAs per SM
+  p3_checks_kernel<Real><<<dim3(gx, CHK_NUM), 256, 0, (cudaStream_t)stream>>>(a);
+  return (int)cudaGetLastError();
+}
+
+template <typename Real>
+int find_loc(const void* field, int64_t stride, int ncol, int nk, double target, unsigned long long* loc_dev, void* stream) {
+  p3_find_loc_kernel<Real><<<grid_for((long long)ncol * nk), 256, 0, (cudaStream_t)stream>>>(
+      (const Real*)field, stride, ncol, nk, target, loc_dev);
+  return (int)cudaGetLastError();
+}
+
+template <typename Real>
+int clip_field(void* field, int64_t stride, int ncol, int nk, double lb, double ub, void* stream) {
+  if (ncol <= 0) return 0;
+  p3_clip_kernel<Real><<<grid_for((long long)ncol * nk), 256, 0, (cudaStream_t)stream>>>(
+      (Real*)field, stride, ncol, nk, (Real)lb, (Real)ub);
+  return (int)cudaGetLastError();
+}
+
 template int preamble_from_abi<double>(const P3B200PreambleFields*, int, int, void*);
 template int preamble_from_abi<float>(const P3B200PreambleFields*, int, int, void*);
-template int postamble_from_abi<double>(const P3B200PostambleFields*, int, int, void*);
-template int postamble_from_abi<float>(const P3B200PostambleFields*, int, int, void*);
+template int postamble_from_abi<double>(const P3B200PostambleFields*, int, int, void*, unsigned*);
+template int postamble_from_abi<float>(const P3B200PostambleFields*, int, int, void*, unsigned*);
+template int checks_from_abi<double>(const P3B200CheckFields*, int, int, void*, unsigned long long*);
+template int checks_from_abi<float>(const P3B200CheckFields*, int, int, void*, unsigned long long*);
+template int find_loc<double>(const void*, int64_t, int, int, double, unsigned long long*, void*);
+template int find_loc<float>(const void*, int64_t, int, int, double, unsigned long long*, void*);
+template int clip_field<double>(void*, int64_t, int, int, double, double, void*);
+template int clip_field<float>(void*, int64_t, int, int, double, double, void*);
 
 }  // namespace p3b200

@@ -66,3 +66,20 @@ POSTAMBLE_OUTPUTS = POSTAMBLE_FIELDS_2D[4:] + POSTAMBLE_FIELDS_1D[2:]
 # compulsory HBM traffic per column-level (arrays read + written once), SURVEY.md §8(f) N1
 PREAMBLE_ARRAYS_RW = (15, 16)
 POSTAMBLE_ARRAYS_RW = (17, 15)
+
+# The property checks P3Microphysics registers (eamxx_p3_process_interface.cpp:226-243), in registration order:
+# (check field, lower bound, upper bound, can_repair).  Names on the left are the C-ABI members of
+# P3B200CheckFields; CHECK_POSTAMBLE_SOURCE maps each to the postamble field that holds it.
+CHECKS = (
+    ("T_mid", 100.0, 500.0, False), ("qv", 1e-13, 0.2, True),
+    ("qc", 0.0, 0.1, False), ("qi", 0.0, 0.1, False), ("qr", 0.0, 0.1, False), ("qm", 0.0, 0.1, False),
+    ("nc", 0.0, 1.0e11, False), ("nr", 0.0, 1.0e10, False), ("ni", 0.0, 1.0e10, False), ("bm", 0.0, 1.0, False),
+    ("precip_liq_surf_mass", 0.0, float.fromhex("0x1.fffffffffffffp+1023"), False),
+    ("precip_ice_surf_mass", 0.0, float.fromhex("0x1.fffffffffffffp+1023"), False),
+    ("eff_radius_qc", 0.0, 1.0e2, False), ("eff_radius_qi", 0.0, 5.0e3, False), ("eff_radius_qr", 0.0, 5.0e3, False),
+)
+CHECK_FIELDS = tuple(c[0] for c in CHECKS)
+CHECK_COLUMN_FIELDS = ("precip_liq_surf_mass", "precip_ice_surf_mass")
+CHECK_POSTAMBLE_SOURCE = {"T_mid": "T_atm", "eff_radius_qc": "diag_eff_radius_qc", "eff_radius_qi": "diag_eff_radius_qi",
+                          "eff_radius_qr": "diag_eff_radius_qr"}
+CHECK_PASS, CHECK_REPAIRABLE, CHECK_FAIL = 0, 1, 2

@@ -10,7 +10,7 @@ import subprocess
 
 import numpy as np
 
-from .fields import (FIELDS, INTERFACE_FIELDS, NUM_DIAG, POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D, PREAMBLE_FIELDS,
+from .fields import (CHECK_COLUMN_FIELDS, CHECK_FIELDS, FIELDS, INTERFACE_FIELDS, NUM_DIAG, POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D, PREAMBLE_FIELDS,
                      RUNTIME_DEFAULTS, SURFACE_1D)
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
@@ -25,6 +25,7 @@ ABI_SYMBOLS = [
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
+    "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv",
     "p3b200_p3_main_f",
 ]
 
@@ -143,6 +144,21 @@ class P3B200PostambleFields(ctypes.Structure):
                  "diag_eff_radius_qc", "diag_eff_radius_qi", "diag_eff_radius_qr", "T_prev", "qv_prev",
                  "precip_liq_surf_flux", "precip_ice_surf_flux", "precip_liq_surf_mass", "precip_ice_surf_mass",
                  "vapor_flux", "water_flux", "ice_flux", "heat_flux")] + [("col_stride", ctypes.c_int64), ("dt", ctypes.c_double)]
+
+
+class P3B200CheckFields(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in CHECK_FIELDS] + [("col_stride", ctypes.c_int64)]
+
+
+class P3B200CheckResult(ctypes.Structure):
+    _fields_ = [("lb", ctypes.c_double), ("ub", ctypes.c_double), ("min_val", ctypes.c_double), ("max_val", ctypes.c_double),
+                ("min_loc", ctypes.c_int64), ("max_loc", ctypes.c_int64), ("result", ctypes.c_int32),
+                ("pass_lower", ctypes.c_int32), ("pass_upper", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+def _check_results(arr):
+    keys = ("lb", "ub", "min_val", "max_val", "min_loc", "max_loc", "result", "pass_lower", "pass_upper")
+    return {name: {k: getattr(arr[i], k) for k in keys} for i, name in enumerate(CHECK_FIELDS)}
 
 
 def make_runtime(overrides=None):
@@ -265,6 +281,12 @@ class P3Handle:
 
     def postamble(self, fields, dt, stream=None):
         """p3_postamble on device tensors (POSTAMBLE_FIELDS_2D + POSTAMBLE_FIELDS_1D; the four boundary fluxes may be absent)."""
+        f = self._postamble_struct(fields, dt)
+        ncol, nlev = fields["qv"].shape
+        check(lib().p3b200_postamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_postamble")
+
+    @staticmethod
+    def _postamble_struct(fields, dt):
         f = P3B200PostambleFields()
         ncol, nlev = fields["qv"].shape
         for n in POSTAMBLE_FIELDS_2D:
@@ -275,7 +297,36 @@ class P3Handle:
             setattr(f, n, fields[n].data_ptr() if n in fields and fields[n] is not None else None)
         f.col_stride = fields["qv"].stride(0)
         f.dt = float(dt)
-        check(lib().p3b200_postamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_postamble")
+        return f
+
+    def postamble_checked(self, fields, dt, stream=None):
+        """p3_postamble with the 15 property checks of the P3 process folded into the same pass.
+        Returns {check name: {lb, ub, min_val, max_val, min_loc, max_loc, result, pass_lower, pass_upper}}."""
+        f = self._postamble_struct(fields, dt)
+        ncol, nlev = fields["qv"].shape
+        out = (P3B200CheckResult * len(CHECK_FIELDS))()
+        check(lib().p3b200_postamble_checked(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
+              "p3b200_postamble_checked")
+        return _check_results(out)
+
+    def property_checks(self, fields, stream=None):
+        """The 15 property checks as one stand-alone pass over device tensors named like CHECK_FIELDS."""
+        f = P3B200CheckFields()
+        ncol, nlev = fields["qv"].shape
+        for n in CHECK_FIELDS:
+            t = fields[n]
+            assert t.is_cuda and (n in CHECK_COLUMN_FIELDS or (t.stride(1) == 1 and t.stride(0) == fields["qv"].stride(0))), n
+            setattr(f, n, t.data_ptr())
+        f.col_stride = fields["qv"].stride(0)
+        out = (P3B200CheckResult * len(CHECK_FIELDS))()
+        check(lib().p3b200_property_checks(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
+              "p3b200_property_checks")
+        return _check_results(out)
+
+    def repair_qv(self, qv, stream=None):
+        ncol, nlev = qv.shape
+        check(lib().p3b200_repair_qv(self._h, ctypes.c_void_p(qv.data_ptr()), ctypes.c_int64(qv.stride(0)), ncol, nlev,
+                                     ctypes.c_void_p(stream or 0)), "p3b200_repair_qv")
 
     def get_diag(self, ncol):
         out = np.empty((ncol, NUM_DIAG), dtype=np.int32)
