@@ -386,6 +386,49 @@ def run_b200(args):
         except Exception as exc:      # never let the side measurement take the headline down
             prepost = {"error": repr(exc)}
 
+    # ---- p3_main + p3_postamble: two calls vs the postamble fused into the tail of phase C, on the bench grid ----
+    if prepost is not None and "error" not in prepost:
+        try:
+            post = {"pmid": fields["pres"], "pseudo_density": fields["dpres"], "th_atm": fields["th"],
+                    "pseudo_density_dry": (fields["dpres"] * (1 - fields["qv"])).contiguous(),
+                    "T_atm": (fields["th"] / fields["inv_exner"]).contiguous(),
+                    "T_prev": torch.empty_like(fields["th"]), "qv_prev": torch.empty_like(fields["th"]),
+                    "precip_liq_surf_flux": fields["precip_liq_surf"], "precip_ice_surf_flux": fields["precip_ice_surf"],
+                    "precip_liq_surf_mass": torch.zeros_like(fields["precip_liq_surf"]),
+                    "precip_ice_surf_mass": torch.zeros_like(fields["precip_ice_surf"])}
+            for n in ("qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm", "diag_eff_radius_qc", "diag_eff_radius_qi",
+                      "diag_eff_radius_qr"):
+                post[n] = fields[n]
+            t_atm0 = post["T_atm"].clone()
+
+            def two_calls():
+                handle.main_prepared(fstruct, infra, stream)
+                handle.postamble(post, dt)
+
+            def fused():
+                handle.main_postamble(fields, post, dt, predict_nc, prescribed_ccn)
+
+            tail = {}
+            for name, fn in (("main_then_postamble", two_calls), ("main_postamble_fused", fused)):
+                ms = []
+                for it in range(4):
+                    restore()
+                    post["T_atm"].copy_(t_atm0)
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    fn()
+                    e1.record()
+                    torch.cuda.synchronize()
+                    if it:                      # first one is the warm-up
+                        ms.append(e0.elapsed_time(e1))
+                tail[name + "_ms"] = sum(ms) / len(ms)
+                tail[name + "_phase_c_ms"] = handle.last_phase_ms()["phase_c"]
+            tail["columns"] = ncol
+            prepost["run_impl_tail"] = tail
+            del post, t_atm0
+        except Exception as exc:
+            prepost["run_impl_tail"] = {"error": repr(exc)}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_oracle_rate(args.ic, nlev, dt, rb, args.cpu_seconds, predict_nc, prescribed_ccn)

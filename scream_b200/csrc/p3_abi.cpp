@@ -7,6 +7,7 @@
 #include "p3_host.hpp"
 #include "p3_kernel.cuh"
 #include "p3_checks.cuh"
+#include "p3_prepost.cuh"
 
 #include <cuda_runtime.h>
 
@@ -138,7 +139,8 @@ int validate(const P3B200Fields* f, const P3B200Infra* in) {
 // Enqueue one kernel launch over `ncol` columns of device arrays.  ev (optional) brackets it.
 template <typename Real>
 int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
-            int ncol, cudaStream_t stream, int* diag, const EventPair* ev) {
+            int ncol, cudaStream_t stream, int* diag, const EventPair* ev, const P3B200PostambleFields* post = nullptr,
+            unsigned* post_mask = nullptr) {
   MainArgs<Real> a;
   for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<Real*>(f->ptr[i]); a.stride[i] = f->col_stride[i]; }
   // common column stride of the 2-D fields (flux arrays apart): enables the one-multiply addressing of the level kernels
@@ -170,15 +172,19 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
     h->cfg_nk = in->nlev; h->cfg_ncol = ncol;
   }
   CU(cudaMemsetAsync(a.queue, 0, QSTRIDE * sizeof(unsigned int), stream));
-  const int rc = launch_main<Real>(a, h->cfg, stream, ev ? reinterpret_cast<void* const*>(ev->m) : nullptr);
+  PostArgs<Real> pa;
+  if (post) pa = make_post_args<Real>(post, ncol, in->nlev, post_mask);
+  const int rc = launch_main<Real>(a, h->cfg, stream, ev ? reinterpret_cast<void* const*>(ev->m) : nullptr,
+                                   post ? &pa : nullptr);
   if (rc) return cuda_fail((cudaError_t)rc, "p3_main_kernel launch");
   return P3B200_OK;
 }
 
 int enqueue_any(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
-                int ncol, cudaStream_t stream, int* diag, const EventPair* ev) {
-  return h->real_bytes == 8 ? enqueue<double>(h, runtime, f, in, ncol, stream, diag, ev)
-                            : enqueue<float>(h, runtime, f, in, ncol, stream, diag, ev);
+                int ncol, cudaStream_t stream, int* diag, const EventPair* ev, const P3B200PostambleFields* post = nullptr,
+                unsigned* post_mask = nullptr) {
+  return h->real_bytes == 8 ? enqueue<double>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask)
+                            : enqueue<float>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask);
 }
 
 }  // namespace
@@ -266,8 +272,9 @@ int p3b200_destroy(p3b200_handle h) {
   return P3B200_OK;
 }
 
-int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
-                const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev) {
+static int main_impl(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                     const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev,
+                     const P3B200PostambleFields* post, unsigned* post_mask) {
   if (!h) return P3B200_EINVAL;
   int rc = validate(fields, infra);
   if (rc) return rc;
@@ -289,7 +296,7 @@ int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Field
   rc = ensure_events(h, 1);
   if (rc) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-  rc = enqueue_any(h, runtime, fields, infra, infra->ncol, stream, diag, &h->events[0]);
+  rc = enqueue_any(h, runtime, fields, infra, infra->ncol, stream, diag, &h->events[0], post, post_mask);
   if (rc) return rc;
   h->events_used = 1;
   if (elapsed_us) {
@@ -299,6 +306,11 @@ int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Field
     *elapsed_us = (int64_t)(ms * 1000.0f + 0.5f);
   }
   return P3B200_OK;
+}
+
+int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev) {
+  return main_impl(h, runtime, fields, infra, cuda_stream, elapsed_us, diag_dev, nullptr, nullptr);
 }
 
 int p3b200_get_diag(p3b200_handle h, int32_t* host_out, int32_t ncol) {
@@ -501,16 +513,12 @@ int p3b200_property_checks(p3b200_handle h, const P3B200CheckFields* f, int32_t 
   return property_checks_impl(h, f, ncol, nlev, out, cuda_stream);
 }
 
-int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
-                             P3B200CheckResult* out, void* cuda_stream) {
-  if (!h || !f || !out) return P3B200_EINVAL;
-  CU(cudaSetDevice(h->device));
+// Read the violation mask a fused postamble left behind and turn it into the 15 results: all Pass when it is zero,
+// else the full reduction over the fields the postamble has just written (extreme values + locations).
+static int checks_from_mask(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
+                            P3B200CheckResult* out, void* cuda_stream) {
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-  if (!h->d_checks) CU(cudaMalloc(&h->d_checks, CHK_STATE_WORDS * sizeof(unsigned long long)));
   unsigned* mask_dev = reinterpret_cast<unsigned*>(h->d_checks + CHK_STATE_MASK);
-  CU(cudaMemsetAsync(mask_dev, 0, sizeof(unsigned), stream));
-  const int rc = postamble_impl(h, f, ncol, nlev, cuda_stream, mask_dev);
-  if (rc) return rc;
   unsigned mask = 0;
   CU(cudaMemcpyAsync(&mask, mask_dev, sizeof(mask), cudaMemcpyDeviceToHost, stream));
   CU(cudaStreamSynchronize(stream));
@@ -535,6 +543,56 @@ int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, in
     if (flagged != (out[i].result != P3B200_CHECK_PASS)) return P3B200_EINTERNAL;
   }
   return P3B200_OK;
+}
+
+int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
+                             P3B200CheckResult* out, void* cuda_stream) {
+  if (!h || !f || !out) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  if (!h->d_checks) CU(cudaMalloc(&h->d_checks, CHK_STATE_WORDS * sizeof(unsigned long long)));
+  unsigned* mask_dev = reinterpret_cast<unsigned*>(h->d_checks + CHK_STATE_MASK);
+  CU(cudaMemsetAsync(mask_dev, 0, sizeof(unsigned), stream));
+  const int rc = postamble_impl(h, f, ncol, nlev, cuda_stream, mask_dev);
+  if (rc) return rc;
+  return checks_from_mask(h, f, ncol, nlev, out, cuda_stream);
+}
+
+// p3_main with p3_postamble fused into the tail of phase C (and, with checks != NULL, the property-check mask).
+int p3b200_main_postamble(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                          const P3B200Infra* infra, const P3B200PostambleFields* post, P3B200CheckResult* checks,
+                          void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev) {
+  if (!h || !fields || !infra || !post) return P3B200_EINVAL;
+  if (!(post->dt > 0) || post->col_stride < infra->nlev) return P3B200_EINVAL;
+  // the tail works on the arrays p3_main has just written: they must be the same arrays, with one column stride
+  struct Alias { const void* p; int f; };
+  const Alias same[] = {{post->th_atm, P3B200_F_TH}, {post->qv, P3B200_F_QV}, {post->qc, P3B200_F_QC}, {post->nc, P3B200_F_NC},
+                        {post->qr, P3B200_F_QR}, {post->nr, P3B200_F_NR}, {post->qi, P3B200_F_QI}, {post->qm, P3B200_F_QM},
+                        {post->ni, P3B200_F_NI}, {post->bm, P3B200_F_BM},
+                        {post->diag_eff_radius_qc, P3B200_F_DIAG_EFF_RADIUS_QC},
+                        {post->diag_eff_radius_qi, P3B200_F_DIAG_EFF_RADIUS_QI},
+                        {post->diag_eff_radius_qr, P3B200_F_DIAG_EFF_RADIUS_QR}};
+  for (const Alias& a : same)
+    if (!a.p || a.p != fields->ptr[a.f] || fields->col_stride[a.f] != post->col_stride) return P3B200_EINVAL;
+  if (post->precip_liq_surf_flux != fields->ptr[P3B200_F_PRECIP_LIQ_SURF] ||
+      post->precip_ice_surf_flux != fields->ptr[P3B200_F_PRECIP_ICE_SURF]) return P3B200_EINVAL;
+  const void* need[] = {post->pmid, post->pseudo_density, post->pseudo_density_dry, post->T_atm, post->T_prev,
+                        post->qv_prev, post->precip_liq_surf_mass, post->precip_ice_surf_mass};
+  for (const void* p : need) if (!p) return P3B200_EINVAL;
+  const int nflux = (post->vapor_flux != nullptr) + (post->water_flux != nullptr) + (post->ice_flux != nullptr) +
+                    (post->heat_flux != nullptr);
+  if (nflux != 0 && nflux != 4) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  unsigned* mask_dev = nullptr;
+  if (checks) {
+    if (!h->d_checks) CU(cudaMalloc(&h->d_checks, CHK_STATE_WORDS * sizeof(unsigned long long)));
+    mask_dev = reinterpret_cast<unsigned*>(h->d_checks + CHK_STATE_MASK);
+    CU(cudaMemsetAsync(mask_dev, 0, sizeof(unsigned), stream));
+  }
+  const int rc = main_impl(h, runtime, fields, infra, cuda_stream, elapsed_us, diag_dev, post, mask_dev);
+  if (rc || !checks) return rc;
+  return checks_from_mask(h, post, infra->ncol, infra->nlev, checks, cuda_stream);
 }
 
 int p3b200_repair_qv(p3b200_handle h, void* qv, int64_t col_stride, int32_t ncol, int32_t nlev, void* cuda_stream) {

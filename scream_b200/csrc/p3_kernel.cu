@@ -19,6 +19,7 @@
 // No __syncthreads anywhere: cross-lane traffic is shuffles/redux inside a warp.  The lookup tables
 // (0.65 MB fp64) are read through the read-only path and stay L2/L1 resident.
 #include "p3_kernel.cuh"
+#include "p3_prepost.cuh"
 
 #include <cuda_runtime.h>
 #include <cstdlib>
@@ -268,6 +269,30 @@ p3_phase_c(const __grid_constant__ MainArgs<Real> a) {
   PhaseC<Real>::template level<UNI>(a, col, k, full == 1);
 }
 
+// Phase C with the p3_postamble of P3Microphysics::run_impl as its tail: the thread that has just written th, the
+// mixing ratios and the radii of (column, level) converts them in place (dry -> wet, T from theta, microns) instead
+// of a second kernel streaming the 32 arrays again.  CHECK also carries the property-check mask (p3_checks.cuh).
+#if !defined(P3B200_CPOST_MINB)
+#define P3B200_CPOST_MINB 8       // measured 4/6/8/10/12 resident CTAs: 70.3/65.3/62.2/63.6/65.1 ms per main+postamble (fp64 spills a few values at 8)
+#endif
+template <typename Real, bool UNI, bool CHECK>
+__global__ void __launch_bounds__(C_THREADS, P3B200_CPOST_MINB)
+p3_phase_c_post(const __grid_constant__ MainArgs<Real> a, const __grid_constant__ PostArgs<Real> p) {
+  const int64_t idx = (int64_t)blockIdx.x * C_THREADS + threadIdx.x;
+  int64_t col;
+  if (idx < (int64_t(1) << 32)) col = (int64_t)((unsigned)idx / (unsigned)a.nk);
+  else col = idx / a.nk;
+  CheckFlags<Real> chk;
+  chk.init();
+  if (col < a.ncol) {
+    const int k = (int)(idx - col * a.nk);
+    const int full = __ldg(a.diag + col * D_NUM + D_HYDRO_PART2);
+    PhaseC<Real>::template level<UNI>(a, col, k, full == 1);
+    postamble_level<Real, CHECK, true>(p, col, k, chk);
+  }
+  if (CHECK) chk.publish(p.check_mask);
+}
+
 template <typename Kernel>
 static int occupancy_blocks(Kernel k, int threads, int smem, int sms, long long need, int* out) {
   int bps = 0;
@@ -339,7 +364,7 @@ static void launch_species(const MainArgs<Real>& a, const LaunchConfig& cfg, cud
 }
 
 template <typename Real>
-int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks) {
+int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks, const PostArgs<Real>* post) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a.ncol <= 0) return 0;
   auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
@@ -358,15 +383,24 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   mark(3);
   launch_species<Real, SP_ICE>(a, cfg, stream);
   mark(4);
-  if (a.ustride != 0 && a.ustride_flux != 0) p3_phase_c<Real, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
-  else p3_phase_c<Real, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  const bool uni = a.ustride != 0 && a.ustride_flux != 0;
+  if (!post) {
+    if (uni) p3_phase_c<Real, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+    else p3_phase_c<Real, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
+  } else if (post->check_mask) {
+    if (uni) p3_phase_c_post<Real, true, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
+    else p3_phase_c_post<Real, false, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
+  } else {
+    if (uni) p3_phase_c_post<Real, true, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
+    else p3_phase_c_post<Real, false, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
+  }
   mark(5);
   return (int)cudaGetLastError();
 }
 
 template int plan_launch<double>(int, int, LaunchConfig*);
 template int plan_launch<float>(int, int, LaunchConfig*);
-template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*);
-template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*);
+template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*, const PostArgs<double>*);
+template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*, const PostArgs<float>*);
 
 }  // namespace p3b200

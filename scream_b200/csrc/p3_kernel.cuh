@@ -24,9 +24,13 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg);
 // Enqueue p3_main for all columns of `a` on `stream` (a cudaStream_t).  `a.queue` must point to
 // 3*NUM_SED_CLASSES zeroed device counters.  Returns a cudaError_t as int.
 // `marks`: optional 6 cudaEvent_t recorded before phase A, after phase A, after each species' sedimentation launches and after phase C (NUM_PHASE_MARKS).
+// `post`: optional p3_postamble arguments (p3_prepost.cuh); when given, phase C runs the postamble of each
+// (column, level) as its tail and no separate postamble launch is needed.
 constexpr int NUM_PHASE_MARKS = 6;
+template <typename Real> struct PostArgs;
 template <typename Real>
-int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks);
+int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks,
+                const PostArgs<Real>* post = nullptr);
 
 // Water/energy budget (p3_budget.cu): per-column values into col_vals[ncol][4], fixed-order two-level sum into
 // totals4 (device).  `partials` holds nparts*4 doubles of scratch.  Returns a cudaError_t as int.

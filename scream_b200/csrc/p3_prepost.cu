@@ -11,22 +11,12 @@
 //   postamble 17 reads + 15 writes                  (256 B in fp64)
 // The helper formulas follow share/util/scream_common_physics_functions_impl.hpp (cited per line).
 #include "p3_kernel.cuh"
-#include "p3_checks.cuh"
+#include "p3_prepost.cuh"
 #include "../../include/p3_b200.h"
 
 #include <cuda_runtime.h>
 
 namespace p3b200 {
-
-template <typename Real>
-struct PrePost {
-  using C = Cst<Real>;
-  // exner_function :88-97
-  static __device__ __forceinline__ Real exner(Real p) { return std::pow(p / C::P0, C::RD * C::INV_CP); }
-  // calculate_drymmr_from_wetmmr_dp_based :375-379 / calculate_wetmmr_from_drymmr_dp_based :327-331
-  static __device__ __forceinline__ Real dry(Real wet, Real pd, Real pdd) { return wet * pd / pdd; }
-  static __device__ __forceinline__ Real wet(Real dry, Real pd, Real pdd) { return dry * pdd / pd; }
-};
 
 template <typename Real>
 struct PreArgs {
@@ -72,78 +62,17 @@ p3_preamble_kernel(const __grid_constant__ PreArgs<Real> a) {
   }
 }
 
-template <typename Real>
-struct PostArgs {
-  const Real *pmid, *pd, *pdd, *th_atm;
-  Real *T_atm, *T_prev, *qv_prev;
-  Real *q[9];                          // qc nc qr nr qi ni qm bm qv  (order of the reference, l.225-233)
-  Real *rad[3];
-  const Real *liq_flux, *ice_flux_in;
-  Real *liq_mass, *ice_mass, *vapor_flux, *water_flux, *ice_flux, *heat_flux;
-  int64_t stride;
-  int ncol, nk;
-  double dt;
-  unsigned* check_mask;                // CHECK only: the violation mask word (p3_checks.cuh)
-};
-
-// CHECK folds the 15 property checks of initialize_impl (:226-243) into the pass: they are evaluated on the values
-// this kernel has just produced (what the reference's post-condition/invariant checks read from memory afterwards).
+// One thread per (column, level); the body is postamble_level (p3_prepost.cuh), shared with the fused tail of phase C.
 template <typename Real, bool CHECK>
 __global__ void __launch_bounds__(256)
 p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
-  using PP = PrePost<Real>;
-  using C = Cst<Real>;
   CheckFlags<Real> chk;
   chk.init();
   const int64_t total = (int64_t)a.ncol * a.nk;
   for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
     const int64_t col = idx / a.nk;
     const int k = (int)(idx - col * a.nk);
-    const int64_t o = col * a.stride + k;
-    const Real pmid = __ldg(a.pmid + o), pd = __ldg(a.pd + o), pdd = __ldg(a.pdd + o);
-    // temperature update with the dry/wet rescaling of dT (l.208-216; calculate_T_from_theta :162-165)
-    const Real T_before = a.T_atm[o];
-    Real T = (__ldg(a.th_atm + o) * PP::exner(pmid) - T_before) * pdd / pd;
-    T += T_before;
-    a.T_atm[o] = T;
-    a.T_prev[o] = T;
-    if (CHECK) chk.template see<CHK_T_MID>(T);
-    // dry -> wet (l.225-234)
-    Real w[9];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) {
-      w[i] = PP::wet(a.q[i][o], pd, pdd);
-      a.q[i][o] = w[i];
-    }
-    a.qv_prev[o] = w[8];
-    // effective radii in microns (l.237-239)
-    Real r[3];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      r[i] = a.rad[i][o] * Real(1e6);
-      a.rad[i][o] = r[i];
-    }
-    if (CHECK) {   // q[] order: qc nc qr nr qi ni qm bm qv
-      chk.template see<CHK_QC>(w[0]); chk.template see<CHK_NC>(w[1]); chk.template see<CHK_QR>(w[2]);
-      chk.template see<CHK_NR>(w[3]); chk.template see<CHK_QI>(w[4]); chk.template see<CHK_NI>(w[5]);
-      chk.template see<CHK_QM>(w[6]); chk.template see<CHK_BM>(w[7]); chk.template see<CHK_QV>(w[8]);
-      chk.template see<CHK_RAD_QC>(r[0]); chk.template see<CHK_RAD_QI>(r[1]); chk.template see<CHK_RAD_QR>(r[2]);
-    }
-    if (k == 0) {
-      // accumulated surface masses and boundary fluxes (l.244-258); m_dt is a double in the reference
-      const Real lf = a.liq_flux[col], icf = a.ice_flux_in[col];
-      const Real lm = Real(a.liq_mass[col] + lf * C::RHO_H2O * a.dt);
-      const Real im = Real(a.ice_mass[col] + icf * C::RHO_H2O * a.dt);
-      a.liq_mass[col] = lm;
-      a.ice_mass[col] = im;
-      if (CHECK) { chk.template see<CHK_PRECIP_LIQ>(lm); chk.template see<CHK_PRECIP_ICE>(im); }
-      if (a.water_flux) {
-        a.vapor_flux[col] = 0;
-        a.water_flux[col] = lf + icf;
-        a.ice_flux[col] = icf;
-        a.heat_flux[col] = 0;
-      }
-    }
+    postamble_level<Real, CHECK, false>(a, col, k, chk);
   }
   if (CHECK) chk.publish(a.check_mask);
 }
@@ -264,7 +193,7 @@ int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* s
   return launch_preamble<Real>(a, stream);
 }
 template <typename Real>
-int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream, unsigned* check_mask) {
+PostArgs<Real> make_post_args(const P3B200PostambleFields* f, int ncol, int nlev, unsigned* check_mask) {
   PostArgs<Real> a;
   a.check_mask = check_mask;
   a.pmid = (const Real*)f->pmid; a.pd = (const Real*)f->pseudo_density; a.pdd = (const Real*)f->pseudo_density_dry;
@@ -277,7 +206,11 @@ int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void*
   a.vapor_flux = (Real*)f->vapor_flux; a.water_flux = (Real*)f->water_flux; a.ice_flux = (Real*)f->ice_flux;
   a.heat_flux = (Real*)f->heat_flux;
   a.stride = f->col_stride; a.ncol = ncol; a.nk = nlev; a.dt = f->dt;
-  return launch_postamble<Real>(a, stream);
+  return a;
+}
+template <typename Real>
+int postamble_from_abi(const P3B200PostambleFields* f, int ncol, int nlev, void* stream, unsigned* check_mask) {
+  return launch_postamble<Real>(make_post_args<Real>(f, ncol, nlev, check_mask), stream);
 }
 
 int checks_reset(unsigned long long* state, int real_bytes, void* stream) {
@@ -317,6 +250,8 @@ int clip_field(void* field, int64_t stride, int ncol, int nk, double lb, double 
 
 template int preamble_from_abi<double>(const P3B200PreambleFields*, int, int, void*);
 template int preamble_from_abi<float>(const P3B200PreambleFields*, int, int, void*);
+template PostArgs<double> make_post_args<double>(const P3B200PostambleFields*, int, int, unsigned*);
+template PostArgs<float> make_post_args<float>(const P3B200PostambleFields*, int, int, unsigned*);
 template int postamble_from_abi<double>(const P3B200PostambleFields*, int, int, void*, unsigned*);
 template int postamble_from_abi<float>(const P3B200PostambleFields*, int, int, void*, unsigned*);
 template int checks_from_abi<double>(const P3B200CheckFields*, int, int, void*, unsigned long long*);

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
-    "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv",
+    "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
 ]
 
@@ -238,6 +238,21 @@ class P3Handle:
         check(lib().p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
                                 ctypes.byref(infra), sptr, ctypes.byref(us) if timed else None, dptr), "p3b200_main")
         return us.value if timed else None
+
+    def main_postamble(self, fields, post_fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None,
+                       zero_flux_top=True, stream=None, checks=False):
+        """p3_main with p3_postamble fused into the tail of phase C (p3b200_main_postamble).  `post_fields` is a
+        postamble dict whose th_atm / mixing ratios / radii / surface fluxes ARE the tensors of `fields`.
+        Returns the 15 check results when checks=True."""
+        f, ncol, nlev = self.fields_struct(fields, host=False)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
+        pf = self._postamble_struct(post_fields, dt)
+        out = (P3B200CheckResult * len(CHECK_FIELDS))() if checks else None
+        check(lib().p3b200_main_postamble(self._h, ctypes.byref(runtime) if runtime is not None else None,
+                                          ctypes.byref(f), ctypes.byref(infra), ctypes.byref(pf), out,
+                                          ctypes.c_void_p(stream) if stream else None, None, None),
+              "p3b200_main_postamble")
+        return _check_results(out) if checks else None
 
     def main_prepared(self, f, infra, stream=None, runtime=None):
         """Hot loop variant for benchmarks: pre-marshalled structs, asynchronous."""

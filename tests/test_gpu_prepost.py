@@ -127,3 +127,67 @@ def test_run_impl_sequence_conserves_wet_water(oracle, p3lib):
     # sequence is compared with the multi-step tolerance class
     assert max(errs.values()) <= 1e-9, {k: v for k, v in errs.items() if v > 1e-9}
     h.close()
+
+
+def _fused_case(torch, p3lib, ic, ncol, nlev, dtype, seed=11):
+    """Device state after the preamble: p3_main fields + the extra postamble arrays; the postamble dict ALIASES the
+    p3_main tensors it shares with them."""
+    from scream_b200 import ic_cases
+    from scream_b200.fields import FIELDS
+    base = (ic_cases.make_mixed_tiled(ncol, nlev, tile=3, dtype=dtype) if ic == "mixed"
+            else ic_cases.make_random(ncol, nlev, dtype=dtype))
+    parity.zero_outputs(base)
+    extra = prepost_cases.make_postamble(ncol, nlev, dtype, seed=seed)
+    main = {n: torch.from_numpy(np.ascontiguousarray(base[n], dtype=dtype)).cuda() for n in FIELDS}
+    post = {n: torch.from_numpy(extra[n]).cuda() for n in ("pseudo_density_dry", "T_prev", "qv_prev", "precip_liq_surf_mass",
+                                                            "precip_ice_surf_mass", "vapor_flux", "water_flux", "ice_flux",
+                                                            "heat_flux")}
+    post["pseudo_density_dry"] = (main["dpres"] * (1 - main["qv"])).contiguous()
+    post["T_atm"] = (main["th"] / main["inv_exner"]).contiguous() + 0.25
+    post.update(pmid=main["pres"], pseudo_density=main["dpres"], th_atm=main["th"],
+                precip_liq_surf_flux=main["precip_liq_surf"], precip_ice_surf_flux=main["precip_ice_surf"])
+    for n in ("qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm", "diag_eff_radius_qc", "diag_eff_radius_qi",
+              "diag_eff_radius_qr"):
+        post[n] = main[n]
+    return main, post
+
+
+@pytest.mark.parametrize("rb,ic,ncol,nlev", [(8, "mixed", 384, 128), (8, "random", 517, 72), (4, "random", 384, 128)])
+def test_fused_main_postamble_is_bit_identical_to_the_two_calls(p3lib, rb, ic, ncol, nlev):
+    """p3b200_main_postamble (postamble as the tail of phase C) == p3b200_main then p3b200_postamble_checked,
+    bit for bit in every array either of them touches, and with the same 15 check results."""
+    torch = pytest.importorskip("torch")
+    dtype = np.float64 if rb == 8 else np.float32
+    h = p3lib.P3Handle(0, rb)
+    m1, p1 = _fused_case(torch, p3lib, ic, ncol, nlev, dtype)
+    h.main(m1, 300.0, True, True)
+    c1 = h.postamble_checked(p1, 300.0)
+    d1 = h.get_diag(ncol)
+    m2, p2 = _fused_case(torch, p3lib, ic, ncol, nlev, dtype)
+    c2 = h.main_postamble(m2, p2, 300.0, True, True, checks=True)
+    d2 = h.get_diag(ncol)
+    assert np.array_equal(d1, d2)
+    for name, a, b in [(n, m1[n], m2[n]) for n in m1] + [(n, p1[n], p2[n]) for n in p1]:
+        assert np.array_equal(a.cpu().numpy(), b.cpu().numpy(), equal_nan=True), name
+    for n in c1:
+        for k in c1[n]:
+            v1, v2 = c1[n][k], c2[n][k]
+            assert v1 == v2 or (v1 != v1 and v2 != v2), (n, k, v1, v2)
+    # without the checks the call stays asynchronous and writes the same arrays
+    m3, p3 = _fused_case(torch, p3lib, ic, ncol, nlev, dtype)
+    assert h.main_postamble(m3, p3, 300.0, True, True) is None
+    torch.cuda.synchronize()
+    for n in p1:
+        assert np.array_equal(p1[n].cpu().numpy(), p3[n].cpu().numpy(), equal_nan=True), n
+    h.close()
+
+
+def test_fused_main_postamble_rejects_foreign_arrays(p3lib):
+    torch = pytest.importorskip("torch")
+    h = p3lib.P3Handle(0, 8)
+    m, p = _fused_case(torch, p3lib, "mixed", 96, 72, np.float64)
+    p = dict(p)
+    p["qc"] = p["qc"].clone()          # not the array p3_main writes
+    with pytest.raises(Exception):
+        h.main_postamble(m, p, 300.0, True, True)
+    h.close()
