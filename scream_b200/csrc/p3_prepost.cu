@@ -15,6 +15,8 @@
 #include "../../include/p3_b200.h"
 
 #include <cuda_runtime.h>
+#include <cstdint>
+#include <initializer_list>
 
 namespace p3b200 {
 
@@ -27,38 +29,69 @@ struct PreArgs {
   int ncol, nk;
 };
 
-template <typename Real>
-__global__ void __launch_bounds__(256)
+// N consecutive levels per thread (N = 2: one 16-byte access per array and thread when levels, stride and base
+// addresses are even), streaming cache hints: every line is touched exactly once.
+template <typename Real, int N> struct PackIO;
+template <typename Real> struct PackIO<Real, 1> {
+  static __device__ __forceinline__ void ld(const Real* p, Real* v) { v[0] = __ldcs(p); }
+  static __device__ __forceinline__ void st(Real* p, const Real* v) { __stcs(p, v[0]); }
+};
+template <> struct PackIO<double, 2> {
+  static __device__ __forceinline__ void ld(const double* p, double* v) {
+    const double2 t = __ldcs(reinterpret_cast<const double2*>(p)); v[0] = t.x; v[1] = t.y;
+  }
+  static __device__ __forceinline__ void st(double* p, const double* v) { __stcs(reinterpret_cast<double2*>(p), make_double2(v[0], v[1])); }
+};
+template <> struct PackIO<float, 2> {
+  static __device__ __forceinline__ void ld(const float* p, float* v) {
+    const float2 t = __ldcs(reinterpret_cast<const float2*>(p)); v[0] = t.x; v[1] = t.y;
+  }
+  static __device__ __forceinline__ void st(float* p, const float* v) { __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1])); }
+};
+
+template <typename Real, int N>
+__global__ void __launch_bounds__(256, 2)
 p3_preamble_kernel(const __grid_constant__ PreArgs<Real> a) {
   using PP = PrePost<Real>;
   using C = Cst<Real>;
-  const int64_t total = (int64_t)a.ncol * a.nk;
+  using IO = PackIO<Real, N>;
+  const int nkp = a.nk / N;                                  // packs per column (N divides nk)
+  const int64_t total = (int64_t)a.ncol * nkp;
   for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
-    const int64_t col = idx / a.nk;
-    const int k = (int)(idx - col * a.nk);
+    const int64_t col = idx / nkp;
+    const int k = (int)(idx - col * nkp) * N;
     const int64_t o = col * a.stride + k;
-    const Real pmid = __ldg(a.pmid + o), pd = __ldg(a.pd + o), pdd = __ldg(a.pdd + o), T = __ldg(a.T_atm + o);
-    const Real cft = __ldg(a.cld_frac_t + o);
-    const Real cft_up = (k != 0) ? __ldg(a.cld_frac_t + o - 1) : Real(0);
-    const Real qv_wet = a.q[0][o];
-    // calculate_dz :400-409 with calculate_virtual_temperature :214-222, on the WET qv (preamble l.78)
-    const Real c1 = -Real(1) + Real(1) / C::ep_2;
-    const Real T_virtual = T * (Real(1) + c1 * qv_wet);
-    a.dz[o] = (C::RD / C::gravit) * pd * T_virtual / pmid;
-    // wet -> dry (l.89-101)
-    a.q[0][o] = PP::dry(qv_wet, pd, pdd);
+    Real pmid[N], pd[N], pdd[N], T[N], cft[N], q[10][N];
+    IO::ld(a.pmid + o, pmid); IO::ld(a.pd + o, pd); IO::ld(a.pdd + o, pdd); IO::ld(a.T_atm + o, T);
+    IO::ld(a.cld_frac_t + o, cft);
+    const Real cft_above = (k != 0) ? __ldg(a.cld_frac_t + o - 1) : Real(0);
 #pragma unroll
-    for (int i = 1; i < 10; ++i) a.q[i][o] = PP::dry(a.q[i][o], pd, pdd);
-    // exner, theta (l.104-107; calculate_theta_from_T :115-118)
-    const Real ex = PP::exner(pmid);
-    a.inv_exner[o] = Real(1.0) / ex;
-    a.th_atm[o] = T / ex;
-    // cloud fractions (l.110-112) and max-overlap rain fraction (l.115-129)
-    const Real mincld = Real(0.0001);
-    const Real cf = cft < mincld ? mincld : cft;
-    a.cld_frac_l[o] = cf;
-    a.cld_frac_i[o] = cf;
-    a.cld_frac_r[o] = (k != 0 && cft_up > cf) ? cft_up : cf;
+    for (int i = 0; i < 10; ++i) IO::ld(a.q[i] + o, q[i]);
+    Real dz[N], inv_ex[N], th[N], cf[N], cfr[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      // calculate_dz :400-409 with calculate_virtual_temperature :214-222, on the WET qv (preamble l.78)
+      const Real c1 = -Real(1) + Real(1) / C::ep_2;
+      const Real T_virtual = T[j] * (Real(1) + c1 * q[0][j]);
+      dz[j] = (C::RD / C::gravit) * pd[j] * T_virtual / pmid[j];
+      // wet -> dry (l.89-101)
+#pragma unroll
+      for (int i = 0; i < 10; ++i) q[i][j] = PP::dry(q[i][j], pd[j], pdd[j]);
+      // exner, theta (l.104-107; calculate_theta_from_T :115-118)
+      const Real ex = PP::exner(pmid[j]);
+      inv_ex[j] = Real(1.0) / ex;
+      th[j] = T[j] / ex;
+      // cloud fractions (l.110-112) and max-overlap rain fraction (l.115-129)
+      const Real mincld = Real(0.0001);
+      cf[j] = cft[j] < mincld ? mincld : cft[j];
+      const Real up = j == 0 ? cft_above : cft[j == 0 ? 0 : j - 1];
+      cfr[j] = (k + j != 0 && up > cf[j]) ? up : cf[j];
+    }
+    IO::st(a.dz + o, dz);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) IO::st(a.q[i] + o, q[i]);
+    IO::st(a.inv_exner + o, inv_ex); IO::st(a.th_atm + o, th);
+    IO::st(a.cld_frac_l + o, cf); IO::st(a.cld_frac_i + o, cf); IO::st(a.cld_frac_r + o, cfr);
   }
 }
 
@@ -73,6 +106,70 @@ p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
     const int64_t col = idx / a.nk;
     const int k = (int)(idx - col * a.nk);
     postamble_level<Real, CHECK, false>(a, col, k, chk);
+  }
+  if (CHECK) chk.publish(a.check_mask);
+}
+
+// The same statements on two consecutive levels per thread with 16-byte streaming accesses (see PackIO).
+template <typename Real, bool CHECK>
+__global__ void __launch_bounds__(256, 2)      // 128 registers: two CTAs per SM also with the check mask (138 unbounded)
+p3_postamble_kernel2(const __grid_constant__ PostArgs<Real> a) {
+  using PP = PrePost<Real>;
+  using C = Cst<Real>;
+  using IO = PackIO<Real, 2>;
+  CheckFlags<Real> chk;
+  chk.init();
+  const int nkp = a.nk / 2;
+  const int64_t total = (int64_t)a.ncol * nkp;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int64_t col = idx / nkp;
+    const int k = (int)(idx - col * nkp) * 2;
+    const int64_t o = col * a.stride + k;
+    Real pmid[2], pd[2], pdd[2], th[2], T[2], w[9][2], r[3][2];
+    IO::ld(a.pmid + o, pmid); IO::ld(a.pd + o, pd); IO::ld(a.pdd + o, pdd); IO::ld(a.th_atm + o, th);
+    IO::ld(a.T_atm + o, T);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) IO::ld(a.q[i] + o, w[i]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) IO::ld(a.rad[i] + o, r[i]);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const Real T_before = T[j];
+      Real Tn = (th[j] * PP::exner(pmid[j]) - T_before) * pdd[j] / pd[j];
+      Tn += T_before;
+      T[j] = Tn;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) w[i][j] = PP::wet(w[i][j], pd[j], pdd[j]);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) r[i][j] = r[i][j] * Real(1e6);
+      if (CHECK) {
+        chk.template see<CHK_T_MID>(Tn);
+        chk.template see<CHK_QC>(w[0][j]); chk.template see<CHK_NC>(w[1][j]); chk.template see<CHK_QR>(w[2][j]);
+        chk.template see<CHK_NR>(w[3][j]); chk.template see<CHK_QI>(w[4][j]); chk.template see<CHK_NI>(w[5][j]);
+        chk.template see<CHK_QM>(w[6][j]); chk.template see<CHK_BM>(w[7][j]); chk.template see<CHK_QV>(w[8][j]);
+        chk.template see<CHK_RAD_QC>(r[0][j]); chk.template see<CHK_RAD_QI>(r[1][j]); chk.template see<CHK_RAD_QR>(r[2][j]);
+      }
+    }
+    IO::st(a.T_atm + o, T); IO::st(a.T_prev + o, T);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) IO::st(a.q[i] + o, w[i]);
+    IO::st(a.qv_prev + o, w[8]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) IO::st(a.rad[i] + o, r[i]);
+    if (k == 0) {
+      const Real lf = a.liq_flux[col], icf = a.ice_flux_in[col];
+      const Real lm = Real(a.liq_mass[col] + lf * C::RHO_H2O * a.dt);
+      const Real im = Real(a.ice_mass[col] + icf * C::RHO_H2O * a.dt);
+      a.liq_mass[col] = lm;
+      a.ice_mass[col] = im;
+      if (CHECK) { chk.template see<CHK_PRECIP_LIQ>(lm); chk.template see<CHK_PRECIP_ICE>(im); }
+      if (a.water_flux) {
+        a.vapor_flux[col] = 0;
+        a.water_flux[col] = lf + icf;
+        a.ice_flux[col] = icf;
+        a.heat_flux[col] = 0;
+      }
+    }
   }
   if (CHECK) chk.publish(a.check_mask);
 }
@@ -101,19 +198,35 @@ p3_checks_kernel(const __grid_constant__ CheckArgs<Real> a) {
   const bool contiguous = stride == nk;
   CheckMinMax<Real> mm;
   mm.init();
-  for (int64_t base = (int64_t)blockIdx.x * 256 + threadIdx.x; base < total; base += 4 * step) {
-    Real v[4];
+  if (contiguous && (total & 1) == 0 && reinterpret_cast<uintptr_t>(f) % (2 * sizeof(Real)) == 0) {
+    // dense field: 16-byte streaming loads, four in flight per thread
+    const int64_t pairs = total >> 1;
+    for (int64_t base = (int64_t)blockIdx.x * 256 + threadIdx.x; base < pairs; base += 4 * step) {
+      Real v[4][2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int64_t idx = base + j * step;
-      v[j] = CheckMinMax<Real>::skipped();
-      if (idx < total) {
-        const int64_t o = contiguous ? idx : (idx / nk) * stride + idx % nk;
-        v[j] = __ldg(f + o);
+      for (int j = 0; j < 4; ++j) {
+        const int64_t idx = base + j * step;
+        v[j][0] = v[j][1] = CheckMinMax<Real>::skipped();
+        if (idx < pairs) PackIO<Real, 2>::ld(f + 2 * idx, v[j]);
       }
-    }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) mm.see(v[j]);
+      for (int j = 0; j < 4; ++j) { mm.see(v[j][0]); mm.see(v[j][1]); }
+    }
+  } else {
+    for (int64_t base = (int64_t)blockIdx.x * 256 + threadIdx.x; base < total; base += 4 * step) {
+      Real v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int64_t idx = base + j * step;
+        v[j] = CheckMinMax<Real>::skipped();
+        if (idx < total) {
+          const int64_t o = contiguous ? idx : (idx / nk) * stride + idx % nk;
+          v[j] = __ldg(f + o);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mm.see(v[j]);
+    }
   }
   mm.template publish<256>(a.state + 2 * fid);
 }
@@ -164,22 +277,42 @@ static int grid_for(long long total) {
   return (int)blocks;
 }
 
+// 16-byte accesses need even levels/stride and 16-byte aligned bases
+template <typename Real>
+static bool pack2_ok(int nk, int64_t stride, std::initializer_list<const void*> ptrs) {
+  if ((nk & 1) || (stride & 1)) return false;
+  for (const void* p : ptrs) if (reinterpret_cast<uintptr_t>(p) % (2 * sizeof(Real))) return false;
+  return true;
+}
+
 template <typename Real>
 int launch_preamble(const PreArgs<Real>& a, void* stream) {
   if (a.ncol <= 0) return 0;
-  p3_preamble_kernel<Real><<<grid_for((long long)a.ncol * a.nk), 256, 0, (cudaStream_t)stream>>>(a);
+  const bool two = pack2_ok<Real>(a.nk, a.stride, {a.pmid, a.pd, a.pdd, a.T_atm, a.cld_frac_t, a.q[0], a.q[1], a.q[2], a.q[3],
+                                                   a.q[4], a.q[5], a.q[6], a.q[7], a.q[8], a.q[9], a.inv_exner, a.th_atm,
+                                                   a.cld_frac_l, a.cld_frac_i, a.cld_frac_r, a.dz});
+  if (two) p3_preamble_kernel<Real, 2><<<grid_for((long long)a.ncol * (a.nk / 2)), 256, 0, (cudaStream_t)stream>>>(a);
+  else p3_preamble_kernel<Real, 1><<<grid_for((long long)a.ncol * a.nk), 256, 0, (cudaStream_t)stream>>>(a);
   return (int)cudaGetLastError();
 }
 template <typename Real>
 int launch_postamble(const PostArgs<Real>& a, void* stream) {
   if (a.ncol <= 0) return 0;
-  const int grid = grid_for((long long)a.ncol * a.nk);
-  if (a.check_mask) p3_postamble_kernel<Real, true><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
-  else p3_postamble_kernel<Real, false><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  const bool two = pack2_ok<Real>(a.nk, a.stride, {a.pmid, a.pd, a.pdd, a.th_atm, a.T_atm, a.T_prev, a.qv_prev, a.q[0], a.q[1],
+                                                   a.q[2], a.q[3], a.q[4], a.q[5], a.q[6], a.q[7], a.q[8], a.rad[0], a.rad[1],
+                                                   a.rad[2]});
+  const int grid = grid_for((long long)a.ncol * (two ? a.nk / 2 : a.nk));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (two) {
+    if (a.check_mask) p3_postamble_kernel2<Real, true><<<grid, 256, 0, st>>>(a);
+    else p3_postamble_kernel2<Real, false><<<grid, 256, 0, st>>>(a);
+  } else {
+    if (a.check_mask) p3_postamble_kernel<Real, true><<<grid, 256, 0, st>>>(a);
+    else p3_postamble_kernel<Real, false><<<grid, 256, 0, st>>>(a);
+  }
   return (int)cudaGetLastError();
 }
 
-// C-struct -> typed arguments (the C ABI structs hold void pointers)
 template <typename Real>
 int preamble_from_abi(const P3B200PreambleFields* f, int ncol, int nlev, void* stream) {
   PreArgs<Real> a;
@@ -227,7 +360,7 @@ int checks_from_abi(const P3B200CheckFields* f, int ncol, int nlev, void* stream
                               f->eff_radius_qr};
   for (int i = 0; i < CHK_NUM; ++i) a.f[i] = (const Real*)src[i];
   a.stride = f->col_stride; a.ncol = ncol; a.nk = nlev; a.state = state;
-  int gx = grid_for(((long long)ncol * nlev + 3) / 4);
+  int gx = grid_for(((long long)ncol * nlev + 7) / 8);
   if (gx > 148 * 8) gx = 148 * 8;       // x CHK_NUM rows: a few waves of 8 resident CTAs per SM
   p3_checks_kernel<Real><<<dim3(gx, CHK_NUM), 256, 0, (cudaStream_t)stream>>>(a);
   return (int)cudaGetLastError();

@@ -20,7 +20,7 @@ def _to_dev(torch, f):
     return {k: torch.from_numpy(v).cuda() for k, v in f.items()}
 
 
-@pytest.mark.parametrize("rb,ncol,nlev", [(8, 517, 128), (8, 3, 72), (4, 517, 128)])
+@pytest.mark.parametrize("rb,ncol,nlev", [(8, 517, 128), (8, 3, 72), (4, 517, 128), (8, 37, 71), (4, 37, 71)])
 def test_preamble_matches_oracle(oracle, p3lib, rb, ncol, nlev):
     torch = pytest.importorskip("torch")
     dtype = np.float64 if rb == 8 else np.float32
@@ -41,11 +41,11 @@ def test_preamble_matches_oracle(oracle, p3lib, rb, ncol, nlev):
     h.close()
 
 
-@pytest.mark.parametrize("rb,with_fluxes", [(8, True), (8, False), (4, True)])
-def test_postamble_matches_oracle(oracle, p3lib, rb, with_fluxes):
+@pytest.mark.parametrize("rb,with_fluxes,nlev", [(8, True, 128), (8, False, 128), (4, True, 128), (8, True, 71), (4, True, 71)])
+def test_postamble_matches_oracle(oracle, p3lib, rb, with_fluxes, nlev):
     torch = pytest.importorskip("torch")
     dtype = np.float64 if rb == 8 else np.float32
-    f = prepost_cases.make_postamble(613, 128, dtype, with_fluxes=with_fluxes)
+    f = prepost_cases.make_postamble(613, nlev, dtype, with_fluxes=with_fluxes)
     ref = {k: v.copy() for k, v in f.items()}
     oracle.postamble(ref, 300.0)
     h = p3lib.P3Handle(0, rb)
