@@ -8,6 +8,8 @@ levels, dt = 300 s, fp64) — the oracle cannot run that many columns in seconds
     diagnostics bit-exact);
   * the global water budget closing to 1e-12 (relative) and no column error bit.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -17,7 +19,8 @@ from tests import parity
 
 pytestmark = pytest.mark.gpu
 
-NCOL, NLEV, DT, TILE = 345600, 128, 300.0, 96
+# P3B200_TEST_FULL_NCOL=1572864 runs the same checks on the ne256pg2 grid (60 GB of fields)
+NCOL, NLEV, DT, TILE = int(os.environ.get("P3B200_TEST_FULL_NCOL", 345600)), 128, 300.0, 96
 
 
 def _device_grid(torch, tile, ncol):
