@@ -18,6 +18,10 @@
 #include <cstdint>
 #include <initializer_list>
 
+#if !defined(P3B200_PP_MINB)
+#define P3B200_PP_MINB 2     // resident 256-thread CTAs per SM the streaming kernels are compiled for
+#endif
+
 namespace p3b200 {
 
 template <typename Real>
@@ -50,7 +54,7 @@ template <> struct PackIO<float, 2> {
 };
 
 template <typename Real, int N>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, P3B200_PP_MINB)
 p3_preamble_kernel(const __grid_constant__ PreArgs<Real> a) {
   using PP = PrePost<Real>;
   using C = Cst<Real>;
@@ -112,7 +116,7 @@ p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
 
 // The same statements on two consecutive levels per thread with 16-byte streaming accesses (see PackIO).
 template <typename Real, bool CHECK>
-__global__ void __launch_bounds__(256, 2)      // 128 registers: two CTAs per SM also with the check mask (138 unbounded)
+__global__ void __launch_bounds__(256, P3B200_PP_MINB)      // 2 -> 128 registers: two CTAs per SM also with the check mask (138 unbounded)
 p3_postamble_kernel2(const __grid_constant__ PostArgs<Real> a) {
   using PP = PrePost<Real>;
   using C = Cst<Real>;
