@@ -116,7 +116,7 @@ p3_postamble_kernel(const __grid_constant__ PostArgs<Real> a) {
 
 // The same statements on two consecutive levels per thread with 16-byte streaming accesses (see PackIO).
 template <typename Real, bool CHECK>
-__global__ void __launch_bounds__(256, P3B200_PP_MINB)      // 2 -> 128 registers: two CTAs per SM also with the check mask (138 unbounded)
+__global__ void __launch_bounds__(256, CHECK ? P3B200_PP_MINB : P3B200_PP_MINB + 1)   // measured 2/3/4 CTAs per SM: plain 3.33/3.05/3.49 ms, with the check mask 3.51/3.54/5.10 ms
 p3_postamble_kernel2(const __grid_constant__ PostArgs<Real> a) {
   using PP = PrePost<Real>;
   using C = Cst<Real>;
