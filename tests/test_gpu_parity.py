@@ -116,6 +116,23 @@ def test_host_path_matches_device_path(oracle, handle64):
     assert np.array_equal(dd, dh)
 
 
+def test_host_path_many_chunks(handle64, p3lib, monkeypatch):
+    """The host pipeline with 1 MB chunks (1024 columns, ragged last chunk, every slot reused several times) equals
+    the device path bit for bit."""
+    monkeypatch.setenv("P3B200_HOST_CHUNK_MB", "1")
+    f = ic_cases.make_random(9973, 72)
+    parity.zero_outputs(f)
+    dev = p3lib.to_device(parity.clone(f))
+    handle64.main(dev, 300.0, True, True)
+    dd = handle64.get_diag(9973)
+    want = p3lib.to_host(dev)
+    got = parity.clone(f)
+    _, dh = handle64.main_host(got, 300.0, True, True)
+    for n in OUTPUTS:
+        assert np.array_equal(want[n], got[n]), n
+    assert np.array_equal(dd, dh)
+
+
 def test_strided_tracer_views(oracle, handle64, p3lib):
     """Tracer fields are sub-views of a bundled (ncol, ntracer, nlev) array: column stride > nlev
     (share/field/field_impl.hpp:880-909)."""
