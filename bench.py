@@ -55,7 +55,31 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-prepost", action="store_true", help="skip the p3_preamble/p3_postamble bandwidth measurement")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
+    ap.add_argument("--flavour", default="product", choices=["product", "parity"],
+                    help="library build: product (ships) or parity (-DP3B200_PARITY, bit-identical to the shared-math oracle)")
+    ap.add_argument("--no-alt", action="store_true", help="skip the second workload line (random-activity IC, G2)")
+    ap.add_argument("--alt-steps", type=int, default=5)
     return ap.parse_args()
+
+
+def host_threads():
+    """Threads the CPU arm may use: the process's CPU affinity, NOT omp_get_max_threads() — torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which throttled the round-1 reference arm to one core at N >= 2."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+CPU_SIMD = "scalar restatement (pack size 1), g++ -O3 -march=x86-64-v3, OpenMP over columns"
+
+
+def workload_config(args, world, ncol_g, ncol, nlev, dt):
+    """The `config` object: identical for the B200 arm and the --impl reference arm (which times a bounded sample of it)."""
+    return {"workload": args.workload, "ic": args.ic, "global_columns": ncol_g, "nlev": nlev, "dt": dt,
+            "columns_per_gpu": ncol, "flags": "predictNc=1,prescribedCCN=1",
+            "parallelism": f"columns block-sharded over {world} GPU(s), no collective in the step",
+            "l2": "inputs 72 GB >> 126 MB L2 and restored (16 GB written) between timed steps"}
 
 
 def make_tile(ic, ncols, nlev, dtype):
@@ -124,16 +148,16 @@ def cpu_oracle_rate(ic, nlev, dt, real_bytes, target_seconds, predict_nc=True, p
     """Time the CPU oracle (all host threads) on a bounded sample of the workload."""
     from tests import oracle_lib
     dtype = np.float64 if real_bytes == 8 else np.float32
-    threads = oracle_lib.max_threads()
+    threads = host_threads()
     probe_cols = 96 * max(threads, 1)
     f = make_tile(ic, probe_cols, nlev, dtype)
-    t, _ = oracle_lib.p3_main(f, dt, predict_nc, prescribed_ccn, want_diag=False)
+    t, _ = oracle_lib.p3_main(f, dt, predict_nc, prescribed_ccn, want_diag=False, nthreads=threads)
     rate = probe_cols / max(t, 1e-9)
     # size the sample for `target_seconds` of CPU WORK (core-seconds), i.e. target/threads of wall
     ncol = int(min(max(rate * target_seconds / max(threads, 1), probe_cols), 400000))
     f = make_tile(ic, ncol, nlev, dtype)
-    t, _ = oracle_lib.p3_main(f, dt, predict_nc, prescribed_ccn, want_diag=False)
-    return {"value": ncol * nlev / t, "unit": UNIT, "cores": threads, "kind": "port",
+    t, _ = oracle_lib.p3_main(f, dt, predict_nc, prescribed_ccn, want_diag=False, nthreads=threads)
+    return {"value": ncol * nlev / t, "unit": UNIT, "cores": threads, "kind": "port", "simd": CPU_SIMD,
             "sample": f"{ncol} columns x {nlev} levels of the '{ic}' IC, dt={dt}, one p3_main call, "
                       f"{t:.3f} s wall on {threads} OpenMP threads (CPU restatement of the reference; "
                       "the reference's Kokkos build cannot be compiled here)"}
@@ -147,9 +171,10 @@ def run_reference(args):
     from tests import oracle_lib
     ncol_g, nlev, dt, rb = WORKLOADS[args.workload]
     dtype = np.float64 if rb == 8 else np.float32
-    threads = oracle_lib.max_threads()
+    threads = host_threads()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     probe = make_tile(args.ic, 64 * threads, nlev, dtype)
-    t, _ = oracle_lib.p3_main(probe, dt, True, True, want_diag=False)
+    t, _ = oracle_lib.p3_main(probe, dt, True, True, want_diag=False, nthreads=threads)
     rate = 64 * threads / max(t, 1e-9)
     # each step ~2 s of wall so that steps+warmup stay within a few minutes
     ncol = int(min(max(rate * 2.0, 64 * threads), 400000))
@@ -157,20 +182,25 @@ def run_reference(args):
     times = []
     for s in range(args.warmup + args.steps):
         f = {k: v.copy() for k, v in base.items()}
-        t, _ = oracle_lib.p3_main(f, dt, True, True, want_diag=False)
+        t, _ = oracle_lib.p3_main(f, dt, True, True, want_diag=False, nthreads=threads)
         if s >= args.warmup:
             times.append(t)
     total = sum(times)
     value = ncol * nlev * len(times) / total
-    sample = (f"{ncol} columns x {nlev} levels of the '{args.ic}' IC per step, dt={dt}, {threads} OpenMP threads; "
-              "CPU restatement (oracle port) of the reference's p3_main — the Kokkos/Fortran reference cannot be built here")
+    sample = (f"{ncol} columns x {nlev} levels of the '{args.ic}' IC per step (a bounded sample of the configured grid), dt={dt}, "
+              f"{threads} OpenMP threads; CPU restatement (oracle port) of the reference's p3_main - the Kokkos/Fortran "
+              "reference cannot be built here (DESIGN.md section 1)")
+    if args.ncol:
+        ncol_g = args.ncol
+    per_gpu = ncol_g if args.scaling == "weak" else (ncol_g // world)
+    glob = ncol_g * world if args.scaling == "weak" else ncol_g
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64" if rb == 8 else "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "ic": args.ic, "nlev": nlev, "dt": dt,
-                       "sample_columns_per_step": ncol, "flags": "predictNc=1,prescribedCCN=1"},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "config": workload_config(args, world, glob, per_gpu, nlev, dt),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "simd": CPU_SIMD,
+                             "sample": sample, "sample_columns_per_step": ncol},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -222,7 +252,7 @@ def run_b200(args):
         for n in zero_names:          # run_impl zero-fills the history arrays; p3_main_f all outputs
             fields[n].zero_()
 
-    handle = p3.P3Handle(local, rb)
+    handle = p3.P3Handle(local, rb, flavour=args.flavour)
     fstruct, _, _ = handle.fields_struct(fields, host=False)
     infra = handle._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, True)
     stream = torch.cuda.current_stream().cuda_stream
@@ -429,6 +459,57 @@ def run_b200(args):
         except Exception as exc:
             prepost["run_impl_tail"] = {"error": repr(exc)}
 
+    # ---- second workload: per-column random activity, 8192 distinct columns.  The headline
+    # IC above tiles 3 distinct columns (the reference's own ic::Factory::mixed), the friendliest input for class-sorted
+    # kernels; this one has load imbalance in every tile, window and work queue.  Same arrays, same timing protocol.
+    alt = None
+    if not args.no_alt and args.ic == "mixed":
+        try:
+            atile_cols = 8192
+            atile = make_tile("random", atile_cols, nlev, dtype)
+            aidx = (torch.arange(ncol, device=dev) + (rank * ncol_g // world if args.scaling == "strong" else 0)) % atile_cols
+            for n in FIELDS:
+                t = torch.from_numpy(atile[n]).to(dev)
+                fields[n].copy_(t.index_select(0, aidx))
+                del t
+            for n in PROGNOSTIC:
+                pristine[n].copy_(fields[n])
+            for _ in range(2):
+                restore()
+                handle.main_prepared(fstruct, infra, stream)
+            barrier()
+            aev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.alt_steps)]
+            for s in range(args.alt_steps):
+                restore()
+                aev[s][0].record()
+                handle.main_prepared(fstruct, infra, stream)
+                aev[s][1].record()
+            barrier()
+            a_ms = [a.elapsed_time(b) for a, b in aev]
+            a_tot = torch.tensor([float(sum(a_ms))], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(a_tot, op=dist.ReduceOp.MAX)
+            a_step = float(a_tot.item()) / args.alt_steps
+            aphases = handle.last_phase_ms()
+            qs = 1e-14
+            active = float(((atile["qc"] >= qs) | (atile["qr"] >= qs) | (atile["qi"] >= qs)).mean())
+            diag = handle.get_diag(min(ncol, atile_cols))
+            edges = [0, 1, 2, 4, 8, 16, 32, 64, 1 << 30]
+            hist = {}
+            for name, col in (("cloud", 5), ("rain", 8), ("ice", 11)):
+                h, _ = np.histogram(diag[:, col], bins=edges)
+                hist[name] = {"bins": "[0,1) [1,2) [2,4) [4,8) [8,16) [16,32) [32,64) [64,inf)", "columns": h.tolist(),
+                              "max": int(diag[:, col].max())}
+            a_ach = bpl * ncol * nlev / (float(sum(a_ms)) / args.alt_steps * 1e-3) / 1e9
+            alt = {"ic": "random (G2: seeded per-column cloud layers, 8192 distinct columns)", "steps": args.alt_steps,
+                   "ms_per_step": a_step, "value": ncol_g * nlev / (a_step * 1e-3), "unit": UNIT,
+                   "roofline_frac": a_ach / peak, "achieved_gbs": a_ach,
+                   "active_level_fraction": active, "substeps_per_column_histogram": hist,
+                   "phase_ms_last_step": {k: round(v, 4) for k, v in aphases.items()},
+                   "column_error_bits": handle.error_summary()}
+        except Exception as exc:
+            alt = {"error": repr(exc)}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_oracle_rate(args.ic, nlev, dt, rb, args.cpu_seconds, predict_nc, prescribed_ccn)
@@ -438,14 +519,11 @@ def run_b200(args):
                 "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f64" if rb == 8 else "f32",
                 "data": "synthetic",
-                "config": {"workload": args.workload, "ic": args.ic, "global_columns": ncol_g, "nlev": nlev,
-                           "dt": dt, "columns_per_gpu": ncol, "flags": "predictNc=1,prescribedCCN=1",
-                           "parallelism": f"columns block-sharded over {world} GPU(s), no collective in the step",
-                           "l2": "inputs 72 GB >> 126 MB L2 and restored (16 GB written) between timed steps"},
+                "config": workload_config(args, world, ncol_g, ncol, nlev, dt), "library_flavour": args.flavour,
                 "roofline": roofline, "run_impl_brackets": prepost, "conservation": budget, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": n_launch * args.steps, "column_error_bits": err_bits,
                 "step_ms": [round(x, 4) for x in step_ms],
-                "phase_ms_last_step": {k: round(v, 4) for k, v in phases.items()}}
+                "phase_ms_last_step": {k: round(v, 4) for k, v in phases.items()}, "alt": alt}
         print(json.dumps(line), flush=True)
     handle.close()
     if world > 1:

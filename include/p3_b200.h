@@ -21,6 +21,7 @@
 #ifndef P3_B200_H
 #define P3_B200_H
 
+#include <stdbool.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -173,8 +174,10 @@ int p3b200_get_diag(p3b200_handle h, int32_t* host_out, int32_t ncol);
 /* OR of diag[P3B200_D_ERROR] over the columns of the last call (synchronises). 0 = clean. */
 int p3b200_error_summary(p3b200_handle h, int32_t* or_of_error_bits);
 
-/* Same as p3b200_main with HOST arrays (same layout): pinned staging, column-chunked H2D -> kernel ->
- * D2H pipeline on internal streams.  This is the shape of P3Microphysics::run_impl for a host-resident
+/* Same as p3b200_main with HOST arrays (same layout): column-chunked H2D -> kernel -> D2H pipeline on internal
+ * streams, copying straight from/to the caller's arrays (no staging copy).  Pass PINNED (page-locked) arrays
+ * (cudaHostAlloc / cudaHostRegister): with pageable memory the copies are staged by the driver and the pipeline
+ * degenerates to synchronous transfers.  This is the shape of P3Microphysics::run_impl for a host-resident
  * field manager and the e2e leg of bench.py.  Returns wall microseconds in elapsed_us. */
 int p3b200_main_host(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* host_fields,
                      const P3B200Infra* infra, int64_t* elapsed_us, int32_t* diag_host);
@@ -182,9 +185,13 @@ int p3b200_main_host(p3b200_handle h, const P3B200Runtime* runtime, const P3B200
 /* Device kernel time (ms) of the last p3b200_main/p3b200_main_host measured with CUDA events on the
  * launching stream(s) (sum over chunks); synchronises. */
 int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches);
-/* The same split by launch: ms5[0] phase A (init+part1+part2), ms5[1..3] cloud/rain/ice sedimentation,
- * ms5[4] phase C (homogeneous freezing + part3); each summed over the chunks of the last call. */
-int p3b200_last_phase_ms(p3b200_handle h, double* ms5);
+/* The same split by phase: ms6[0] phase A (init+part1+part2), ms6[1..3] cloud/rain/ice sedimentation, ms6[4] phase C
+ * (homogeneous freezing + part3), ms6[5] the whole sedimentation stage (end of phase A to start of phase C); each
+ * summed over the chunks of the last call.  p3b200_main runs the three species side by side on helper streams of the
+ * handle (they share no data; environment P3B200_SED_SERIAL=1 restores stream order): ms6[1..3] are then each species'
+ * time since the end of phase A, and p3b200_last_sed_concurrent returns 1. */
+int p3b200_last_phase_ms(p3b200_handle h, double* ms6);
+int p3b200_last_sed_concurrent(p3b200_handle h);
 
 /* ---- global water / energy budget (the one collective of the path: the caller all-reduces 4 doubles) ------
  * Domain totals over the columns of `fields` (device arrays), formed in double in a fixed order:
@@ -308,7 +315,7 @@ int p3b200_p3_main_f(
   double* nc_nuceat_tend, double* nccn_prescribed, double* ni_activated, double* inv_qc_relvar, int it,
   double* precip_liq_surf, double* precip_ice_surf, int its, int ite, int kts, int kte,
   double* diag_eff_radius_qc, double* diag_eff_radius_qi, double* diag_eff_radius_qr, double* rho_qi,
-  int do_predict_nc, int do_prescribed_CCN, double* dpres, double* inv_exner,
+  bool do_predict_nc, bool do_prescribed_CCN, double* dpres, double* inv_exner,
   double* qv2qi_depos_tend, double* precip_liq_flux, double* precip_ice_flux,
   double* cld_frac_r, double* cld_frac_l, double* cld_frac_i,
   double* liq_ice_exchange, double* vap_liq_exchange, double* vap_ice_exchange,

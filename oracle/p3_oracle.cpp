@@ -15,6 +15,7 @@
 using namespace p3o;
 
 double p3o::pm::g_scale[p3o::pm::NUM_FN] = {1, 1, 1, 1, 1, 1, 1, 1};
+int p3o::pm::g_shared = 0;
 
 namespace {
 
@@ -244,3 +245,38 @@ extern "C" void p3o_set_math_scale(const double* scale8) {
   for (int i = 0; i < p3o::pm::NUM_FN; ++i) p3o::pm::g_scale[i] = scale8 ? scale8[i] : 1.0;
 }
 
+// 0: host libm (default), 1: the deterministic transcendentals shared with the kernels (p3_math.hpp)
+extern "C" void p3o_set_math_mode(int shared) { p3o::pm::g_shared = shared ? 1 : 0; }
+extern "C" int p3o_get_math_mode() { return p3o::pm::g_shared; }
+
+// Evaluate one transcendental family (pm::Fn order) of the shared header on arrays: tests/test_cpu_shared_math.py
+// measures its error against mpmath.  real_bytes 4 evaluates the binary32 overloads (inputs/outputs still double).
+extern "C" void p3o_math_eval(int fn, int real_bytes, int n, const double* x, const double* y, double* out) {
+  for (int i = 0; i < n; ++i) {
+    if (real_bytes == 8) {
+      const double a = x[i], b = y ? y[i] : 0.0;
+      switch (fn) {
+        case p3o::pm::POW: out[i] = p3math::pow(a, b); break;
+        case p3o::pm::EXP: out[i] = p3math::exp(a); break;
+        case p3o::pm::LOG: out[i] = p3math::log(a); break;
+        case p3o::pm::LOG10: out[i] = p3math::log10(a); break;
+        case p3o::pm::CBRT: out[i] = p3math::cbrt(a); break;
+        case p3o::pm::TGAMMA: out[i] = p3math::tgamma(a); break;
+        case p3o::pm::TANH: out[i] = p3math::tanh(a); break;
+        default: out[i] = p3math::expm1(a); break;
+      }
+    } else {
+      const float a = (float)x[i], b = y ? (float)y[i] : 0.0f;
+      switch (fn) {
+        case p3o::pm::POW: out[i] = p3math::pow(a, b); break;
+        case p3o::pm::EXP: out[i] = p3math::exp(a); break;
+        case p3o::pm::LOG: out[i] = p3math::log(a); break;
+        case p3o::pm::LOG10: out[i] = p3math::log10(a); break;
+        case p3o::pm::CBRT: out[i] = p3math::cbrt(a); break;
+        case p3o::pm::TGAMMA: out[i] = p3math::tgamma(a); break;
+        case p3o::pm::TANH: out[i] = p3math::tanh(a); break;
+        default: out[i] = p3math::expm1(a); break;
+      }
+    }
+  }
+}

@@ -11,6 +11,7 @@
 // per level, columns and levels in the reference's loop order.  Parity unpinned like the rest of the oracle:
 // the reference stores no expected outputs for these functors.
 #include "p3_oracle_types.hpp"
+#include "p3_oracle_math.hpp"
 
 #include <cmath>
 #include <cstdint>
@@ -20,7 +21,7 @@ namespace {
 template <typename Real>
 struct PF {
   using C = p3o::Constants<Real>;
-  static Real exner_function(Real pressure) { return std::pow(pressure / C::P0, C::RD * C::INV_CP); }
+  static Real exner_function(Real pressure) { return p3o::pm::pow(pressure / C::P0, C::RD * C::INV_CP); }
   static Real calculate_theta_from_T(Real temperature, Real pressure) { return temperature / exner_function(pressure); }
   static Real calculate_T_from_theta(Real theta, Real pressure) { return theta * exner_function(pressure); }
   static Real calculate_virtual_temperature(Real temperature, Real qv) {

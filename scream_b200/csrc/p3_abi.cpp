@@ -75,6 +75,10 @@ struct p3b200_ctx {
   unsigned long long* d_checks = nullptr;   // 2*CHK_NUM min/max keys + 2 location slots (property checks)
   double* d_budget = nullptr;     // [budget_cols][4] per-column values + BUDGET_PARTS*4 partials + 4 totals
   size_t budget_cols = 0;
+  // helper streams/events that let the three sedimentation species run side by side (p3_kernel.cuh: SideStreams)
+  cudaStream_t side_stream[2] = {nullptr, nullptr};
+  cudaEvent_t side_event[3] = {nullptr, nullptr, nullptr};
+  bool sed_concurrent = false;    // what the last p3b200_main did
 };
 
 namespace {
@@ -141,7 +145,7 @@ int validate(const P3B200Fields* f, const P3B200Infra* in) {
 template <typename Real>
 int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
             int ncol, cudaStream_t stream, int* diag, const EventPair* ev, const P3B200PostambleFields* post = nullptr,
-            unsigned* post_mask = nullptr) {
+            unsigned* post_mask = nullptr, bool allow_side = false) {
   MainArgs<Real> a;
   for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<Real*>(f->ptr[i]); a.stride[i] = f->col_stride[i]; }
   // common column stride of the 2-D fields (flux arrays apart): enables the one-multiply addressing of the level kernels
@@ -175,17 +179,20 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
   CU(cudaMemsetAsync(a.queue, 0, QSTRIDE * sizeof(unsigned int), stream));
   PostArgs<Real> pa;
   if (post) pa = make_post_args<Real>(post, ncol, in->nlev, post_mask);
+  SideStreams side{{h->side_stream[0], h->side_stream[1]}, h->side_event[0], {h->side_event[1], h->side_event[2]}};
+  const bool use_side = allow_side && h->side_stream[0] && !std::getenv("P3B200_SED_SERIAL");
+  h->sed_concurrent = use_side;
   const int rc = launch_main<Real>(a, h->cfg, stream, ev ? reinterpret_cast<void* const*>(ev->m) : nullptr,
-                                   post ? &pa : nullptr);
+                                   post ? &pa : nullptr, use_side ? &side : nullptr);
   if (rc) return cuda_fail((cudaError_t)rc, "p3_main_kernel launch");
   return P3B200_OK;
 }
 
 int enqueue_any(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, const P3B200Infra* in,
                 int ncol, cudaStream_t stream, int* diag, const EventPair* ev, const P3B200PostambleFields* post = nullptr,
-                unsigned* post_mask = nullptr) {
-  return h->real_bytes == 8 ? enqueue<double>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask)
-                            : enqueue<float>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask);
+                unsigned* post_mask = nullptr, bool allow_side = false) {
+  return h->real_bytes == 8 ? enqueue<double>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask, allow_side)
+                            : enqueue<float>(h, runtime, f, in, ncol, stream, diag, ev, post, post_mask, allow_side);
 }
 
 }  // namespace
@@ -249,6 +256,16 @@ int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p
     e = cudaMalloc(&h->d_queue, NQUEUE * QSTRIDE * sizeof(unsigned int));
     if (e != cudaSuccess) rc = cuda_fail(e, "cudaMalloc queue");
   }
+  if (rc == P3B200_OK) {
+    for (int i = 0; i < 2 && rc == P3B200_OK; ++i) {
+      e = cudaStreamCreateWithFlags(&h->side_stream[i], cudaStreamNonBlocking);
+      if (e != cudaSuccess) rc = cuda_fail(e, "cudaStreamCreate side");
+    }
+    for (int i = 0; i < 3 && rc == P3B200_OK; ++i) {
+      e = cudaEventCreateWithFlags(&h->side_event[i], cudaEventDisableTiming);
+      if (e != cudaSuccess) rc = cuda_fail(e, "cudaEventCreate side");
+    }
+  }
   if (rc != P3B200_OK) { p3b200_destroy(h); return rc; }
   *out = h;
   return P3B200_OK;
@@ -264,6 +281,8 @@ int p3b200_destroy(p3b200_handle h) {
     if (s.diag) cudaFree(s.diag);
     if (s.stream) cudaStreamDestroy(s.stream);
   }
+  for (auto& st : h->side_stream) if (st) cudaStreamDestroy(st);
+  for (auto& evn : h->side_event) if (evn) cudaEventDestroy(evn);
   if (h->d_tables) cudaFree(h->d_tables);
   if (h->d_diag) cudaFree(h->d_diag);
   if (h->d_queue) cudaFree(h->d_queue);
@@ -297,7 +316,7 @@ static int main_impl(p3b200_handle h, const P3B200Runtime* runtime, const P3B200
   rc = ensure_events(h, 1);
   if (rc) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-  rc = enqueue_any(h, runtime, fields, infra, infra->ncol, stream, diag, &h->events[0], post, post_mask);
+  rc = enqueue_any(h, runtime, fields, infra, infra->ncol, stream, diag, &h->events[0], post, post_mask, true);
   if (rc) return rc;
   h->events_used = 1;
   if (elapsed_us) {
@@ -606,20 +625,26 @@ int p3b200_repair_qv(p3b200_handle h, void* qv, int64_t col_stride, int32_t ncol
   return P3B200_OK;
 }
 
-int p3b200_last_phase_ms(p3b200_handle h, double* ms5) {
-  if (!h || !ms5) return P3B200_EINVAL;
+int p3b200_last_phase_ms(p3b200_handle h, double* ms6) {
+  if (!h || !ms6) return P3B200_EINVAL;
   CU(cudaSetDevice(h->device));
-  for (int p = 0; p < EV_END; ++p) ms5[p] = 0;
+  for (int p = 0; p < 6; ++p) ms6[p] = 0;
+  // marks: 0 start, 1 phase A done, 2/3/4 cloud/rain/ice done, 5 joined, 6 end (p3_kernel.cuh)
+  const bool conc = h->sed_concurrent;
+  const int from[6] = {0, 1, conc ? 1 : 2, conc ? 1 : 3, 5, 1};
+  const int to[6]   = {1, 2, 3, 4, 6, 5};
   for (size_t i = 0; i < h->events_used; ++i) {
     CU(cudaEventSynchronize(h->events[i].m[EV_END]));
-    for (int p = 0; p < EV_END; ++p) {
+    for (int p = 0; p < 6; ++p) {
       float t = 0;
-      CU(cudaEventElapsedTime(&t, h->events[i].m[p], h->events[i].m[p + 1]));
-      ms5[p] += t;
+      CU(cudaEventElapsedTime(&t, h->events[i].m[from[p]], h->events[i].m[to[p]]));
+      ms6[p] += t;
     }
   }
   return P3B200_OK;
 }
+
+int p3b200_last_sed_concurrent(p3b200_handle h) { return (h && h->sed_concurrent) ? 1 : 0; }
 
 }  // extern "C"
 

@@ -467,7 +467,7 @@ struct Sediment {
           const Real dum = sp(1.496e-6) * P::pow1p5(T0) / (T0 + 120);
           fac[j] = C::gravit * C::RHO_H2O / (18 * dum);
         } else if (SP == SP_RAIN) {
-          fac[j] = std::pow(C::RHO_1000MB * inv_rho[j], sp(.54));   // rhofacr, p3_main_impl_part1.hpp:105
+          fac[j] = P::x_pow(C::RHO_1000MB * inv_rho[j], sp(.54));   // rhofacr, p3_main_impl_part1.hpp:105
         } else {
           fac[j] = -1;    // rhofaci (p3_main_impl_part1.hpp:106) is evaluated when the level first holds ice
         }
@@ -490,7 +490,12 @@ struct Sediment {
     // interpolation weight is exactly 0 (integral mu_r) the bilinear form reduces bit for bit to the linear
     // interpolation along the size axis, read from the (vm, vn)-interleaved slice `rain_tab`
     // (the caller passes rain_tab only when that holds: p3_sediment checks the weight once per CTA)
+#if defined(P3B200_EXACT_MATH)
+    const bool rain_fast = false;       // exact-order build: get_rain_dsd2 + lookup + apply_table as the reference calls them
+    (void)rain_tab;
+#else
     const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr;
+#endif
 
     // rain, fast-table path: the in-cloud values of the NEXT sub-step are carried in registers (what
     // calculate_incloud_mixingratios left after part2 for the first one, q*(1/cld_frac) afterwards), and the
@@ -542,26 +547,30 @@ struct Sediment {
         if (SP == SP_ICE) {
           // rhofaci for the whole slot the first time any of its levels holds ice (one pow per slot and column, not
           // one per sub-step as the front advances level by level); all lanes of the warp take part in the vote
-          if (w.any(fac[j] < 0 && k <= k_qxbot && q[j] > 0)) { if (fac[j] < 0) fac[j] = std::pow(C::RHO_600MB * inv_rho[j], sp(.54)); }
+          if (w.any(fac[j] < 0 && k <= k_qxbot && q[j] > 0)) { if (fac[j] < 0) fac[j] = P::x_pow(C::RHO_600MB * inv_rho[j], sp(.54)); }
         }
         if (k <= k_qxbot) {
           if (SP == SP_CLOUD) {
             Real qc_i, nc_i;
             if (first) P::incloud_liq(q[j], n[j], icf[j], qc_i, nc_i);
+#if defined(P3B200_EXACT_MATH)
+            else { qc_i = q[j] / cf[j]; nc_i = n[j] / cf[j]; }       // p3_cloud_sed_impl.hpp:124-125
+#else
             else { qc_i = q[j] * icf[j]; nc_i = n[j] * icf[j]; }
+#endif
             if (qc_i > qsmall) {
               Real mu_c, lamc, d0, d1;
               P::template cloud_dsd2<true>(qc_i, nc_i, rho[j], mu_c, lamc, d0, d1, false);
               n[j] = nc_i * cf[j];
               const Real acn = fac[j];
               // bcn = 2: pow(lamc, bcn) = lamc*lamc exactly for IEEE pow with an integral exponent 2
-              const Real dum = 1 / (lamc * lamc);
+              const Real dum = 1 / P::pow_bcn(lamc);
               // bcn = 2: Gamma(4+bcn+mu)/Gamma(mu+4) = (mu+5)(mu+4) and Gamma(1+bcn+mu)/Gamma(mu+1) = (mu+2)(mu+1)
               // exactly; the products are within 1 ulp of the true quotient, closer than the quotient of two
               // library tgamma values the reference forms (4 tgamma calls were 40 % of this kernel's instructions)
 #if defined(P3B200_EXACT_MATH)
-              vq = acn * std::tgamma(4 + C::bcn + mu_c) * dum / std::tgamma(mu_c + 4);
-              if (predictNc) vn = acn * std::tgamma(1 + C::bcn + mu_c) * dum / std::tgamma(mu_c + 1);
+              vq = acn * P::x_tgamma(4 + C::bcn + mu_c) * dum / P::x_tgamma(mu_c + 4);
+              if (predictNc) vn = acn * P::x_tgamma(1 + C::bcn + mu_c) * dum / P::x_tgamma(mu_c + 1);
 #else
               vq = acn * ((mu_c + 5) * (mu_c + 4)) * dum;
               if (predictNc) vn = acn * ((mu_c + 2) * (mu_c + 1)) * dum;
@@ -569,6 +578,18 @@ struct Sediment {
             }
           } else if (SP == SP_RAIN) {
             Real qr_i = q_in[j], nr_i = n_in[j];
+#if defined(P3B200_EXACT_MATH)
+            if (qr_i > qsmall) {
+              // compute_rain_fall_velocity (p3_rain_sed_impl.hpp:17-34) statement by statement
+              Real mu_r_k = 0, lamr;
+              P::rain_dsd2(qr_i, nr_i, mu_r_k, lamr, a.ro);
+              typename P::Loc3 t3;
+              P::lookup3(mu_r_k, lamr, t3);
+              vq = P::apply_table3(a.tb.vm, t3) * fac[j];
+              vn = P::apply_table3(a.tb.vn, t3) * fac[j];
+              n[j] = nr_i * cf[j];
+            }
+#else
             if (qr_i > qsmall) {
               // get_rain_dsd2 + compute_rain_fall_velocity (p3_dsd2_impl.hpp:76-127, p3_rain_sed_impl.hpp:17-34)
               const Real nr_lim = P::rmax(nr_i, C::NSMALL);
@@ -598,6 +619,7 @@ struct Sediment {
               }
               n[j] = nr_i * cf[j];
             }
+#endif
           } else {
             Real qi_i, ni_i, qm_i, bm_i;
             if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / cflw[j], qi_i, ni_i, qm_i, bm_i);
@@ -643,7 +665,11 @@ struct Sediment {
         prt_local = (k == kbot && k_qxbot == kbot) ? prt_new : prt_local;
         // precip_liq_flux(k+1) += flux_qx(k) for k in [k_qxtop, new k_qxbot], p3_rain_sed_impl.hpp:139-153
         // (flux is exactly 0 outside that range and acc >= 0, so the add needs no guard)
+#if defined(P3B200_EXACT_MATH)
+        if (SP == SP_RAIN) { acc[j] = acc[j] + flux[j]; q_in[j] = q[j] / cf[j]; n_in[j] = n[j] / cf[j]; }   // p3_rain_sed_impl.hpp:133-134
+#else
         if (SP == SP_RAIN) { acc[j] = acc[j] + flux[j]; q_in[j] = q[j] * icf[j]; n_in[j] = n[j] * icf[j]; }
+#endif
       }
       if (k_qxbot != kbot) k_qxbot += 1;
       dt_left -= dt_sub;
@@ -664,13 +690,15 @@ struct Sediment {
     const Real surf = prt_accum * C::INV_RHO_H2O * inv_dt;
     err = w.or_int(err);
     if (lane == 0) {
-      // launches run in stream order cloud -> rain -> ice, so these read-modify-writes never race
-      if (SP == SP_CLOUD) a.f[F_PRECIP_LIQ_SURF][col] = surf;                 // assignment, p3_cloud_sed_impl.hpp:134
-      if (SP == SP_RAIN)  a.f[F_PRECIP_LIQ_SURF][col] += surf;                // p3_rain_sed_impl.hpp:157
-      if (SP == SP_ICE)   a.f[F_PRECIP_ICE_SURF][col] += surf;                // p3_ice_sed_impl.hpp:192
+      // The three species' launches may run concurrently (p3_kernel.cu: launch_main).  precip_liq_surf is zeroed by
+      // phase A, assigned by cloud (p3_cloud_sed_impl.hpp:134) and incremented by rain (p3_rain_sed_impl.hpp:157):
+      // (0 + c) + r == (0 + r) + c bit for bit (IEEE addition commutes, 0 + x is exact), so both ADD atomically.
+      if (SP == SP_CLOUD) WP::atomic_add(a.f[F_PRECIP_LIQ_SURF] + col, surf);
+      if (SP == SP_RAIN)  WP::atomic_add(a.f[F_PRECIP_LIQ_SURF] + col, surf);
+      if (SP == SP_ICE)   a.f[F_PRECIP_ICE_SURF][col] += surf;                // p3_ice_sed_impl.hpp:192 (only ice writes it)
       int* d = a.diag + col * D_NUM;
       d[dbase + 1] = k_qxbot; d[dbase + 2] = nsub;
-      if (err) d[D_ERROR] |= err;
+      if (err) WP::atomic_or(d + D_ERROR, err);
     }
   }
 };

@@ -51,15 +51,15 @@ Runtime<Real> make_runtime(const P3B200Runtime& r) {
   o.do_ice_production = r.do_ice_production ? 1 : 0;
   // p3_autoconversion_impl.hpp:30-36
   if (o.autoconversion_radius == Real(25.0e-6)) o.autoconv_cons3 = C::CONS3;
-  else o.autoconv_cons3 = Real(1.0) / (C::CONS2 * std::pow(o.autoconversion_radius, Real(3.0)));
+  else o.autoconv_cons3 = Real(1.0) / (C::CONS2 * P::x_pow(o.autoconversion_radius, Real(3.0)));
   // MurphyKoop_svp(Tmelt, liquid): physics_saturation_impl.hpp:62-71 at T = 273.15
   const Real tm = C::Tmelt;
-  o.svp_liq_tmelt = P::svp_liquid(tm, std::log(tm));
+  o.svp_liq_tmelt = P::svp_liquid(tm, P::x_log(tm));
   const Real mu_r = o.constant_mu_rain;
-  o.gamma_mur_p1 = std::tgamma(mu_r + 1);
-  o.gamma_mur_p2 = std::tgamma(mu_r + 2);
-  o.lgamma7_mur = std::log(std::tgamma(Real(7.) + mu_r));
-  o.lgamma4_mur = std::log(std::tgamma(Real(4.) + mu_r));
+  o.gamma_mur_p1 = P::x_tgamma(mu_r + 1);
+  o.gamma_mur_p2 = P::x_tgamma(mu_r + 2);
+  o.lgamma7_mur = P::x_log(P::x_tgamma(Real(7.) + mu_r));
+  o.lgamma4_mur = P::x_log(P::x_tgamma(Real(4.) + mu_r));
   return o;
 }
 

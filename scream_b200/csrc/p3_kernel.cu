@@ -1,23 +1,22 @@
 // p3_kernel.cu — the sm_100a kernels of libp3b200: p3_main for a batch of columns.
 //
-// Execution model (replaces the Kokkos TeamPolicy of p3_main_impl.hpp:86-113, one team per column,
-// all phases in one kernel separated by team barriers).  p3_main is a short sequence of launches on one stream:
+// Execution model (replaces the Kokkos TeamPolicy of p3_main_impl.hpp:86-113, one team per column, all phases in
+// one kernel separated by team barriers).  p3_main is a short sequence of launches:
 //
-//   p3_phase_a   init + part1 + part2.  One WARP per column, the 32 lanes stride over the levels, so
-//                every global access of a warp is one contiguous 256-byte (fp64) row segment.  Level
-//                parallel, register heavy (255 regs), no serial dependency between levels.
+//   p3_phase_a   init + part1 + part2 for one tile of columns per CTA (4 warps).  Pass 1: one thread per level,
+//                coalesced along the column, classifies the level (or finishes it when part2 has nothing to do);
+//                a counting sort by process class in shared memory; pass 2: warps pull groups of 32 same-class
+//                levels and run the fused part1+part2 on them.  Block barriers separate the passes.
 //   p3_sediment<cloud|rain|ice, JW>
-//                CFL sub-stepped sedimentation, one launch per species and window class (JW = 1,2,4,8
-//                register slots per lane).  One warp per column that holds the species, window of
-//                reachable levels in registers, warp shuffles for the upwind flux, redux for the Courant
-//                maximum.  Persistent warps pull chunks of columns from an atomic counter, which absorbs
-//                the load imbalance (columns with rain need tens of sub-steps, most need none).  Few
-//                registers per thread -> 3-8x the resident warps of phase A to hide the latency of the
-//                serial sub-step chain.
+//                CFL sub-stepped sedimentation, one launch per species and window class (JW = 1,2,4,8 register
+//                slots per lane).  One warp per column that holds the species, window of reachable levels in
+//                registers, warp shuffles for the upwind flux, redux for the Courant maximum.  Persistent warps
+//                pull chunks of columns from an atomic counter, which absorbs the load imbalance.  The three
+//                species share no data and run side by side on helper streams (launch_main).
 //   p3_phase_c   homogeneous freezing + part3.  One THREAD per (column, level).
 //
-// No __syncthreads anywhere: cross-lane traffic is shuffles/redux inside a warp.  The lookup tables
-// (0.65 MB fp64) are read through the read-only path and stay L2/L1 resident.
+// The lookup tables (0.65 MB fp64) are read through the read-only path and stay L2/L1 resident; the rain
+// fall-speed slice is staged in shared memory.
 #include "p3_kernel.cuh"
 #include "p3_prepost.cuh"
 
@@ -48,6 +47,8 @@ struct WarpDev {
   __device__ __forceinline__ int max_int(int v) const { return __reduce_max_sync(FULL, v); }
   __device__ __forceinline__ int or_int(int v) const { return (int)__reduce_or_sync(FULL, (unsigned)v); }
   __device__ __forceinline__ void sync() const { __syncwarp(); }
+  template <class R> static __device__ __forceinline__ void atomic_add(R* p, R v) { atomicAdd(p, v); }
+  static __device__ __forceinline__ void atomic_or(int* p, int v) { atomicOr(p, v); }
   // value of the previous lane (lane 0 keeps its own: callers patch it) / of lane `src`
   template <class R> __device__ __forceinline__ R shfl_up1(R v) const { return __shfl_up_sync(FULL, v, 1); }
   template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
@@ -364,25 +365,44 @@ static void launch_species(const MainArgs<Real>& a, const LaunchConfig& cfg, cud
 }
 
 template <typename Real>
-int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks, const PostArgs<Real>* post) {
+int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks, const PostArgs<Real>* post,
+                const SideStreams* side) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a.ncol <= 0) return 0;
-  auto mark = [&](int i) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], stream); };
-  mark(0);
+  auto mark = [&](int i, cudaStream_t s) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], s); };
+  mark(0, stream);
   {
     const bool uni = a.ustride != 0 && a.ustride_flux != 0;
 #define P3_LAUNCH_A(OCC, UNI) p3_phase_a<Real, OCC, UNI><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic)
     if (uni) P3_LAUNCH_A(A_MIN_BLOCKS, true); else P3_LAUNCH_A(A_MIN_BLOCKS, false);
 #undef P3_LAUNCH_A
   }
-  mark(1);
-  // stream order cloud -> rain -> ice: precip_liq_surf is assigned by cloud and incremented by rain
-  launch_species<Real, SP_CLOUD>(a, cfg, stream);
-  mark(2);
-  launch_species<Real, SP_RAIN>(a, cfg, stream);
-  mark(3);
-  launch_species<Real, SP_ICE>(a, cfg, stream);
-  mark(4);
+  mark(1, stream);
+  if (side) {
+    // rain (the longest, issue-bound) stays on the caller's stream; ice and cloud (latency-bound) run beside it
+    cudaStream_t s_ice = (cudaStream_t)side->stream[0], s_cloud = (cudaStream_t)side->stream[1];
+    cudaEventRecord((cudaEvent_t)side->fork, stream);
+    cudaStreamWaitEvent(s_ice, (cudaEvent_t)side->fork, 0);
+    cudaStreamWaitEvent(s_cloud, (cudaEvent_t)side->fork, 0);
+    launch_species<Real, SP_RAIN>(a, cfg, stream);
+    mark(3, stream);
+    launch_species<Real, SP_ICE>(a, cfg, s_ice);
+    mark(4, s_ice);
+    cudaEventRecord((cudaEvent_t)side->join[0], s_ice);
+    launch_species<Real, SP_CLOUD>(a, cfg, s_cloud);
+    mark(2, s_cloud);
+    cudaEventRecord((cudaEvent_t)side->join[1], s_cloud);
+    cudaStreamWaitEvent(stream, (cudaEvent_t)side->join[0], 0);
+    cudaStreamWaitEvent(stream, (cudaEvent_t)side->join[1], 0);
+  } else {
+    launch_species<Real, SP_CLOUD>(a, cfg, stream);
+    mark(2, stream);
+    launch_species<Real, SP_RAIN>(a, cfg, stream);
+    mark(3, stream);
+    launch_species<Real, SP_ICE>(a, cfg, stream);
+    mark(4, stream);
+  }
+  mark(5, stream);
   const bool uni = a.ustride != 0 && a.ustride_flux != 0;
   if (!post) {
     if (uni) p3_phase_c<Real, true><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a);
@@ -394,13 +414,13 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
     if (uni) p3_phase_c_post<Real, true, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
     else p3_phase_c_post<Real, false, false><<<cfg.c_blocks, C_THREADS, 0, stream>>>(a, *post);
   }
-  mark(5);
+  mark(6, stream);
   return (int)cudaGetLastError();
 }
 
 template int plan_launch<double>(int, int, LaunchConfig*);
 template int plan_launch<float>(int, int, LaunchConfig*);
-template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*, const PostArgs<double>*);
-template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*, const PostArgs<float>*);
+template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*, const PostArgs<double>*, const SideStreams*);
+template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*, const PostArgs<float>*, const SideStreams*);
 
 }  // namespace p3b200

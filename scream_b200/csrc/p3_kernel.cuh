@@ -23,14 +23,20 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg);
 
 // Enqueue p3_main for all columns of `a` on `stream` (a cudaStream_t).  `a.queue` must point to
 // 3*NUM_SED_CLASSES zeroed device counters.  Returns a cudaError_t as int.
-// `marks`: optional 6 cudaEvent_t recorded before phase A, after phase A, after each species' sedimentation launches and after phase C (NUM_PHASE_MARKS).
+// `marks`: optional NUM_PHASE_MARKS cudaEvent_t: [0] before phase A, [1] after phase A, [2] cloud / [3] rain / [4] ice
+// sedimentation finished, [5] all three joined (phase C may start), [6] after phase C.
+// `side`: optional two helper streams + three events owned by the caller.  The three species share no data except
+// precip_liq_surf (cloud and rain both add into it, atomically; phase A zeroes it): with `side` the ice and cloud
+// launches run on the helper streams beside the rain launches (rain is bound by instruction issue, ice by latency),
+// joined by events before phase C.  Without it the launches are serial on `stream`.
 // `post`: optional p3_postamble arguments (p3_prepost.cuh); when given, phase C runs the postamble of each
 // (column, level) as its tail and no separate postamble launch is needed.
-constexpr int NUM_PHASE_MARKS = 6;
+constexpr int NUM_PHASE_MARKS = 7;
+struct SideStreams { void* stream[2]; void* fork; void* join[2]; };   // cudaStream_t x2, cudaEvent_t x3
 template <typename Real> struct PostArgs;
 template <typename Real>
 int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks,
-                const PostArgs<Real>* post = nullptr);
+                const PostArgs<Real>* post = nullptr, const SideStreams* side = nullptr);
 
 // Water/energy budget (p3_budget.cu): per-column values into col_vals[ncol][4], fixed-order two-level sum into
 // totals4 (device).  `partials` holds nparts*4 doubles of scratch.  Returns a cudaError_t as int.

@@ -36,7 +36,7 @@ template <typename Real>
 struct PrePost {
   using C = Cst<Real>;
   // exner_function :88-97
-  static __device__ __forceinline__ Real exner(Real p) { return std::pow(p / C::P0, C::RD * C::INV_CP); }
+  static __device__ __forceinline__ Real exner(Real p) { return Phys<Real>::x_pow(p / C::P0, C::RD * C::INV_CP); }
   // calculate_drymmr_from_wetmmr_dp_based :375-379 / calculate_wetmmr_from_drymmr_dp_based :327-331
   static __device__ __forceinline__ Real dry(Real wet, Real pd, Real pdd) { return wet * pd / pdd; }
   static __device__ __forceinline__ Real wet(Real dry, Real pd, Real pdd) { return dry * pdd / pd; }

@@ -15,6 +15,10 @@ from .fields import (CHECK_COLUMN_FIELDS, CHECK_FIELDS, FIELDS, INTERFACE_FIELDS
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("P3B200_LIB", os.path.join(PKG_DIR, "libp3b200.so"))   # override: development only
+# Build flavours of the same sources (scream_b200/csrc/Makefile): "product" is what ships; "parity" is compiled with
+# -DP3B200_PARITY (the reference's operation order everywhere + the deterministic transcendentals of p3_math.hpp) and
+# has to agree with the shared-math oracle bit for bit on every column (tests/test_gpu_parity_all_columns.py).
+LIB_PATHS = {"product": LIB_PATH, "parity": os.path.join(PKG_DIR, "libp3b200_parity.so")}
 TABLE_BLOB = os.path.join(PKG_DIR, "data", "p3_lookup_table_1.v4.1.1.f64")
 NUM_FIELDS = len(FIELDS)
 
@@ -24,6 +28,7 @@ ABI_SYMBOLS = [
     "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
+    "p3b200_last_sed_concurrent",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
@@ -59,7 +64,7 @@ class P3Error(RuntimeError):
     pass
 
 
-_lib = None
+_libs = {}
 
 
 def build(force=False):
@@ -70,13 +75,13 @@ def build(force=False):
     subprocess.check_call(["make", "-C", csrc, "-s"])
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise P3Error(f"{LIB_PATH} is missing: build it with `make -C scream_b200/csrc` "
+def lib(flavour="product"):
+    if flavour not in _libs:
+        path = LIB_PATHS[flavour]
+        if not os.path.exists(path):
+            raise P3Error(f"{path} is missing: build it with `make -C scream_b200/csrc` "
                           "(there is no CPU fallback for p3_main)")
-        L = ctypes.CDLL(LIB_PATH)
+        L = ctypes.CDLL(path)
         L.p3b200_strerror.restype = ctypes.c_char_p
         L.p3b200_last_cuda_error.restype = ctypes.c_char_p
         L.p3b200_runtime_defaults.restype = None
@@ -94,6 +99,7 @@ def lib():
         L.p3b200_last_kernel_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
                                             ctypes.POINTER(ctypes.c_int64)]
         L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
+        L.p3b200_last_sed_concurrent.argtypes = [ctypes.c_void_p]
         L.p3b200_water_energy_totals.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
@@ -102,9 +108,9 @@ def lib():
         L.p3b200_tables_generate_rain.argtypes = [ctypes.POINTER(P3B200Tables)]
         dp = ctypes.POINTER(ctypes.c_double)
         L.p3b200_p3_main_f.argtypes = ([dp] * 6 + [ctypes.c_double] + [dp] * 10 + [ctypes.c_int] + [dp] * 2 +
-                                       [ctypes.c_int] * 4 + [dp] * 4 + [ctypes.c_int] * 2 + [dp] * 13)
-        _lib = L
-    return _lib
+                                       [ctypes.c_int] * 4 + [dp] * 4 + [ctypes.c_bool] * 2 + [dp] * 13)
+        _libs[flavour] = L
+    return _libs[flavour]
 
 
 def check(rc, what="p3b200"):
@@ -179,16 +185,18 @@ def _levels(name, nlev):
 class P3Handle:
     """Owns one p3b200 handle (device tables + diagnostics) on one GPU."""
 
-    def __init__(self, device=0, real_bytes=8, tables=None):
+    def __init__(self, device=0, real_bytes=8, tables=None, flavour="product"):
+        self._L = lib(flavour)
+        self.flavour = flavour
         self._h = ctypes.c_void_p()
         self.real_bytes = real_bytes
         self.device = device
         t = tables if tables is not None else load_tables()
-        check(lib().p3b200_create(ctypes.byref(t), device, real_bytes, ctypes.byref(self._h)), "p3b200_create")
+        check(self._L.p3b200_create(ctypes.byref(t), device, real_bytes, ctypes.byref(self._h)), "p3b200_create")
 
     def close(self):
         if self._h:
-            lib().p3b200_destroy(self._h)
+            self._L.p3b200_destroy(self._h)
             self._h = ctypes.c_void_p()
 
     def __del__(self):
@@ -235,7 +243,7 @@ class P3Handle:
         us = ctypes.c_int64(0)
         sptr = ctypes.c_void_p(stream) if stream else None
         dptr = ctypes.c_void_p(diag.data_ptr()) if diag is not None else None
-        check(lib().p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+        check(self._L.p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
                                 ctypes.byref(infra), sptr, ctypes.byref(us) if timed else None, dptr), "p3b200_main")
         return us.value if timed else None
 
@@ -248,7 +256,7 @@ class P3Handle:
         infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
         pf = self._postamble_struct(post_fields, dt)
         out = (P3B200CheckResult * len(CHECK_FIELDS))() if checks else None
-        check(lib().p3b200_main_postamble(self._h, ctypes.byref(runtime) if runtime is not None else None,
+        check(self._L.p3b200_main_postamble(self._h, ctypes.byref(runtime) if runtime is not None else None,
                                           ctypes.byref(f), ctypes.byref(infra), ctypes.byref(pf), out,
                                           ctypes.c_void_p(stream) if stream else None, None, None),
               "p3b200_main_postamble")
@@ -256,7 +264,7 @@ class P3Handle:
 
     def main_prepared(self, f, infra, stream=None, runtime=None):
         """Hot loop variant for benchmarks: pre-marshalled structs, asynchronous."""
-        check(lib().p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+        check(self._L.p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
                                 ctypes.byref(infra), ctypes.c_void_p(stream) if stream else None, None, None),
               "p3b200_main")
 
@@ -267,7 +275,7 @@ class P3Handle:
         infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
         us = ctypes.c_int64(0)
         diag = np.full((ncol, NUM_DIAG), -7, dtype=np.int32) if want_diag else None
-        check(lib().p3b200_main_host(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
+        check(self._L.p3b200_main_host(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
                                      ctypes.byref(infra), ctypes.byref(us),
                                      diag.ctypes.data if want_diag else None), "p3b200_main_host")
         return us.value, diag
@@ -278,7 +286,7 @@ class P3Handle:
         f, ncol, nlev = self.fields_struct(fields, host=False)
         infra = self._infra(ncol, nlev, dt, True, True, True)
         out = np.zeros(4, dtype=np.float64)
-        check(lib().p3b200_water_energy_totals(self._h, ctypes.byref(f), ctypes.byref(infra),
+        check(self._L.p3b200_water_energy_totals(self._h, ctypes.byref(f), ctypes.byref(infra),
                                                ctypes.c_void_p(stream) if stream else None, None, out.ctypes.data),
               "p3b200_water_energy_totals")
         return out
@@ -292,13 +300,13 @@ class P3Handle:
             assert t.is_cuda and t.stride(1) == 1 and t.stride(0) == fields["qv"].stride(0), n
             setattr(f, n, t.data_ptr())
         f.col_stride = fields["qv"].stride(0)
-        check(lib().p3b200_preamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_preamble")
+        check(self._L.p3b200_preamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_preamble")
 
     def postamble(self, fields, dt, stream=None):
         """p3_postamble on device tensors (POSTAMBLE_FIELDS_2D + POSTAMBLE_FIELDS_1D; the four boundary fluxes may be absent)."""
         f = self._postamble_struct(fields, dt)
         ncol, nlev = fields["qv"].shape
-        check(lib().p3b200_postamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_postamble")
+        check(self._L.p3b200_postamble(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_void_p(stream or 0)), "p3b200_postamble")
 
     @staticmethod
     def _postamble_struct(fields, dt):
@@ -320,7 +328,7 @@ class P3Handle:
         f = self._postamble_struct(fields, dt)
         ncol, nlev = fields["qv"].shape
         out = (P3B200CheckResult * len(CHECK_FIELDS))()
-        check(lib().p3b200_postamble_checked(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
+        check(self._L.p3b200_postamble_checked(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
               "p3b200_postamble_checked")
         return _check_results(out)
 
@@ -334,36 +342,39 @@ class P3Handle:
             setattr(f, n, t.data_ptr())
         f.col_stride = fields["qv"].stride(0)
         out = (P3B200CheckResult * len(CHECK_FIELDS))()
-        check(lib().p3b200_property_checks(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
+        check(self._L.p3b200_property_checks(self._h, ctypes.byref(f), ncol, nlev, out, ctypes.c_void_p(stream or 0)),
               "p3b200_property_checks")
         return _check_results(out)
 
     def repair_qv(self, qv, stream=None):
         ncol, nlev = qv.shape
-        check(lib().p3b200_repair_qv(self._h, ctypes.c_void_p(qv.data_ptr()), ctypes.c_int64(qv.stride(0)), ncol, nlev,
+        check(self._L.p3b200_repair_qv(self._h, ctypes.c_void_p(qv.data_ptr()), ctypes.c_int64(qv.stride(0)), ncol, nlev,
                                      ctypes.c_void_p(stream or 0)), "p3b200_repair_qv")
 
     def get_diag(self, ncol):
         out = np.empty((ncol, NUM_DIAG), dtype=np.int32)
-        check(lib().p3b200_get_diag(self._h, out.ctypes.data, ncol), "p3b200_get_diag")
+        check(self._L.p3b200_get_diag(self._h, out.ctypes.data, ncol), "p3b200_get_diag")
         return out
 
     def error_summary(self):
         v = ctypes.c_int32(0)
-        check(lib().p3b200_error_summary(self._h, ctypes.byref(v)), "p3b200_error_summary")
+        check(self._L.p3b200_error_summary(self._h, ctypes.byref(v)), "p3b200_error_summary")
         return v.value
 
     def last_kernel_ms(self):
         ms = ctypes.c_double(0)
         n = ctypes.c_int64(0)
-        check(lib().p3b200_last_kernel_ms(self._h, ctypes.byref(ms), ctypes.byref(n)), "p3b200_last_kernel_ms")
+        check(self._L.p3b200_last_kernel_ms(self._h, ctypes.byref(ms), ctypes.byref(n)), "p3b200_last_kernel_ms")
         return ms.value, n.value
 
     def last_phase_ms(self):
-        """Device ms of the five launches of the last call: phase A, cloud/rain/ice sedimentation, phase C."""
-        ms = (ctypes.c_double * 5)()
-        check(lib().p3b200_last_phase_ms(self._h, ms), "p3b200_last_phase_ms")
-        return dict(zip(("phase_a", "sed_cloud", "sed_rain", "sed_ice", "phase_c"), [float(x) for x in ms]))
+        """Device ms of the phases of the last call: phase A, cloud/rain/ice sedimentation, phase C, and the whole
+        sedimentation stage (the species run side by side unless P3B200_SED_SERIAL=1, see include/p3_b200.h)."""
+        ms = (ctypes.c_double * 6)()
+        check(self._L.p3b200_last_phase_ms(self._h, ms), "p3b200_last_phase_ms")
+        out = dict(zip(("phase_a", "sed_cloud", "sed_rain", "sed_ice", "phase_c", "sed_stage"), [float(x) for x in ms]))
+        out["sed_concurrent"] = int(self._L.p3b200_last_sed_concurrent(self._h))
+        return out
 
 
 def to_device(fields, device="cuda:0"):

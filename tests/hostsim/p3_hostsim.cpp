@@ -18,6 +18,8 @@ struct WarpSim {
   int max_int(int v) const { return v; }
   int or_int(int v) const { return v; }
   void sync() const {}
+  template <class R> static void atomic_add(R* p, R v) { *p = *p + v; }
+  static void atomic_or(int* p, int v) { *p |= v; }
   template <class R> R shfl_up1(R v) const { return v; }
   template <class R> R shfl_from(R v, int) const { return v; }
 };

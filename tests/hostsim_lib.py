@@ -18,12 +18,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = [os.path.join(ROOT, "tests", "hostsim", "p3_hostsim.cpp"),
        os.path.join(ROOT, "scream_b200", "csrc", "p3_host.cpp")]
 DEPS = SRC + [os.path.join(ROOT, "scream_b200", "csrc", f) for f in
-              ("p3_column.cuh", "p3_physics.cuh", "p3_host.hpp")] + [os.path.join(ROOT, "include", "p3_b200.h")]
+              ("p3_column.cuh", "p3_physics.cuh", "p3_host.hpp", "p3_math.hpp")] + [os.path.join(ROOT, "include", "p3_b200.h")]
 # two flavours: "exact" (-DP3B200_EXACT_MATH: the reference's own pow calls, comparable with the oracle to
 # the last bit -> proves the driver logic) and "product" (the arithmetic the GPU build uses, which replaces a
 # few pow calls by 1-ulp-equivalent cheaper forms -> compared on the well-conditioned columns)
+# "parity" (-DP3B200_PARITY = exact order + the shared deterministic transcendentals of p3_math.hpp): has to match
+# the oracle in shared-math mode BIT FOR BIT on every column; it is the CPU twin of libp3b200_parity.so
 LIB_PATHS = {"exact": os.path.join(ROOT, "build", "libp3hostsim_exact.so"),
-             "product": os.path.join(ROOT, "build", "libp3hostsim.so")}
+             "product": os.path.join(ROOT, "build", "libp3hostsim.so"),
+             "parity": os.path.join(ROOT, "build", "libp3hostsim_parity.so")}
 
 _libs = {}
 _tables = None
@@ -34,8 +37,8 @@ def build(flavour="exact"):
     stale = (not os.path.exists(path)) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in DEPS)
     if stale:
         os.makedirs(os.path.dirname(path), exist_ok=True)
-        extra = ["-DP3B200_EXACT_MATH"] if flavour == "exact" else []
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared",
+        extra = {"exact": ["-DP3B200_EXACT_MATH"], "parity": ["-DP3B200_PARITY"], "product": []}[flavour]
+        subprocess.check_call(["g++", "-O2", "-march=x86-64-v3", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared",
                                "-I/usr/local/cuda/include"] + extra + ["-o", path] + SRC)
 
 

@@ -49,6 +49,11 @@ def lib():
         L.p3o_max_threads.restype = ctypes.c_int
         L.p3o_set_math_scale.restype = None
         L.p3o_set_math_scale.argtypes = [ctypes.c_void_p]
+        L.p3o_set_math_mode.restype = None
+        L.p3o_set_math_mode.argtypes = [ctypes.c_int]
+        L.p3o_get_math_mode.restype = ctypes.c_int
+        L.p3o_math_eval.restype = None
+        L.p3o_math_eval.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -137,6 +142,27 @@ def set_math_scale(scale=None):
     arr = np.full(len(MATH_FUNCS), scale, dtype=np.float64) if np.isscalar(scale) else np.asarray(scale, dtype=np.float64)
     assert arr.shape == (len(MATH_FUNCS),)
     lib().p3o_set_math_scale(arr.ctypes.data)
+
+
+def set_math_mode(mode):
+    """'libm': the host's std:: math (what the reference's CPU build calls); 'shared': the deterministic
+    transcendentals of scream_b200/csrc/p3_math.hpp that the kernels are built with (-DP3B200_SHARED_MATH)."""
+    assert mode in ("libm", "shared")
+    lib().p3o_set_math_mode(1 if mode == "shared" else 0)
+
+
+def math_mode():
+    return "shared" if lib().p3o_get_math_mode() else "libm"
+
+
+def math_eval(fn, x, y=None, real_bytes=8):
+    """Evaluate transcendental `fn` (a name in MATH_FUNCS) of the shared header on arrays."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    out = np.empty_like(x)
+    yy = np.ascontiguousarray(y, dtype=np.float64) if y is not None else None
+    lib().p3o_math_eval(MATH_FUNCS.index(fn), real_bytes, x.size, x.ctypes.data,
+                        yy.ctypes.data if yy is not None else None, out.ctypes.data)
+    return out
 
 
 def max_threads():

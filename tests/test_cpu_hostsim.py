@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 from scream_b200 import ic_cases
-from tests import hostsim_lib, parity
+from tests import hostsim_lib, oracle_lib, parity
 
 FLAGS = [(False, False), (False, True), (True, False), (True, True)]
 
@@ -90,3 +90,23 @@ def test_single_level_and_single_column(oracle):
     for n in parity.OUTPUTS:
         np.testing.assert_allclose(got[n], ref[n], rtol=1e-13, atol=0, err_msg=n)
     assert np.array_equal(d_ref, d_got)
+
+
+@pytest.mark.parametrize("nlev,dt,dtype", [(72, 1800.0, np.float64), (128, 300.0, np.float64), (128, 300.0, np.float32)])
+def test_parity_flavour_is_bit_identical_to_the_shared_math_oracle(nlev, dt, dtype):
+    """-DP3B200_PARITY (reference operation order + p3_math.hpp) vs the oracle switched to the same header: every
+    output of every random column bit for bit, integer diagnostics included — the CPU twin of
+    tests/test_gpu_parity_all_columns.py."""
+    from scream_b200.fields import OUTPUTS
+    oracle_lib.set_math_mode("shared")
+    try:
+        f = ic_cases.make_random(1024, nlev, dtype=dtype)
+        parity.zero_outputs(f)
+        ref, got = parity.clone(f), parity.clone(f)
+        _, d_ref = oracle_lib.p3_main(ref, dt, True, True)
+        d_got = hostsim_lib.p3_main(got, dt, True, True, flavour="parity")
+    finally:
+        oracle_lib.set_math_mode("libm")
+    for n in OUTPUTS:
+        assert np.array_equal(ref[n], got[n], equal_nan=True), n
+    assert np.array_equal(d_ref[:, :12], d_got[:, :12])
