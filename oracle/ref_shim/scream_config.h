@@ -15,7 +15,9 @@
 #define SCREAM_NUM_VERTICAL_LEV 72
 #define SCREAM_TEST_LEVEL 0
 #define SCREAM_MPI_ON_DEVICE 0
+#ifndef SCREAM_DATA_DIR
 #define SCREAM_DATA_DIR "."
+#endif
 #define EAMXX_GIT_VERSION "ref"
 #define EAMXX_VERSION "0.0.0"
 #endif

@@ -1,9 +1,9 @@
 #!/usr/bin/env python
 """Generate the regression fixtures under tests/golden/ from the oracle.
 
-The reference ships no expected outputs for p3_main and cannot be run here, so these
-files do NOT pin the oracle to the reference; they pin the oracle (and through it the CUDA path) to
-ITSELF across commits: any change of the restatement's results shows up as a diff of these files.
+These files pin the oracle (and through it the CUDA path) to ITSELF across commits, integer diagnostics included: any
+change of the restatement's results shows up as a diff.  The fixtures that pin the oracle to the REFERENCE are the
+ref_*.npz files written by tools/make_ref_golden.py from the reference's own code (oracle/_ref).
 Case: ic::Factory::mixed(3, 72), dt = 300, one p3_main call, the four (predictNc, prescribedCCN)
 combinations — the reference's p3_run_and_cmp protocol (p3/tests/p3_run_and_cmp.cpp:218-352), first step.
 
