@@ -191,6 +191,9 @@ int p3b200_last_kernel_ms(p3b200_handle h, double* ms, int64_t* launches);
  * handle (they share no data; environment P3B200_SED_SERIAL=1 restores stream order): ms6[1..3] are then each species'
  * time since the end of phase A, and p3b200_last_sed_concurrent returns 1. */
 int p3b200_last_phase_ms(p3b200_handle h, double* ms6);
+/* Split of phase A (ms6[0]) over its three kernels: ms3[0] classification pass (streaming: init + the deciding part of
+ * part1 on every level), ms3[1] the part2 launches (one per process group), ms3[2] the column finish. */
+int p3b200_last_phase_a_ms(p3b200_handle h, double* ms3);
 int p3b200_last_sed_concurrent(p3b200_handle h);
 
 /* ---- global water / energy budget (the one collective of the path: the caller all-reduces 4 doubles) ------

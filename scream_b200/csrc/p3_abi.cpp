@@ -38,12 +38,12 @@ int cuda_fail(cudaError_t e, const char* what) {
   } while (0)
 
 constexpr int NQUEUE = 64;        // ring of work-queue counter groups so p3_main calls in flight on different streams never share one
-constexpr int QSTRIDE = 16;       // counters per group: one per sedimentation launch (3 species x NUM_SED_CLASSES) + pad
+constexpr int QSTRIDE = 32;       // counters per group: one per sedimentation launch (3 species x NUM_SED_CLASSES), one per part2 group, pad
 constexpr int NSLOT = 3;          // host pipeline depth (H2D / kernel / D2H in flight)
 
 // events around and between the five launches of one p3_main: m[0] = start, m[EV_END] = end
 struct EventPair { cudaEvent_t m[NUM_PHASE_MARKS] = {nullptr}; };
-constexpr int EV_END = NUM_PHASE_MARKS - 1;
+constexpr int EV_END = PHASE_MARK_END;
 
 struct Slot {                     // one in-flight column chunk of p3b200_main_host
   cudaStream_t stream = nullptr;
@@ -65,6 +65,13 @@ struct p3b200_ctx {
   size_t diag_cols = 0;
   unsigned int* d_queue = nullptr;
   int next_queue = 0;
+  // phase-A scratch (work lists, per-level flag bytes: p3_kernel.cuh ScratchLayout), grown on demand.  One copy per
+  // handle: a call's classification pass waits (scratch_free) until the previous call's column finish has run, so
+  // calls on different streams (the host pipeline's slots) never overlap in it.
+  void* d_scratch = nullptr;
+  size_t scratch_bytes = 0;
+  cudaEvent_t scratch_free = nullptr;
+  bool scratch_pending = false;
   std::vector<EventPair> events;  // one pair per kernel launch of the last call
   size_t events_used = 0;
   int last_ncol = 0;
@@ -76,8 +83,8 @@ struct p3b200_ctx {
   double* d_budget = nullptr;     // [budget_cols][4] per-column values + BUDGET_PARTS*4 partials + 4 totals
   size_t budget_cols = 0;
   // helper streams/events that let the three sedimentation species run side by side (p3_kernel.cuh: SideStreams)
-  cudaStream_t side_stream[2] = {nullptr, nullptr};
-  cudaEvent_t side_event[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t side_stream[NUM_SIDE_STREAMS] = {};
+  cudaEvent_t side_event[NUM_SIDE_STREAMS + 1] = {};
   bool sed_concurrent = false;    // what the last p3b200_main did
 };
 
@@ -164,6 +171,7 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
   }
   a.ncol = ncol; a.nk = in->nlev; a.dt = Real(in->dt);
   a.predictNc = in->predictNc; a.prescribedCCN = in->prescribedCCN; a.zero_flux_top = in->zero_flux_top;
+  a.history_prezeroed = 0;   // p3b200_main makes no assumption about the history arrays (run_impl-level callers zero them and say so)
   if constexpr (sizeof(Real) == 8) a.tb = h->tbd; else a.tb = h->tbf;
   P3B200Runtime r;
   if (runtime) r = *runtime; else runtime_defaults(r);
@@ -177,14 +185,32 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
     h->cfg_nk = in->nlev; h->cfg_ncol = ncol;
   }
   CU(cudaMemsetAsync(a.queue, 0, QSTRIDE * sizeof(unsigned int), stream));
+  {
+    const ScratchLayout sl = scratch_layout(ncol, in->nlev, h->cfg.a_tile_cols);
+    if (sl.total > h->scratch_bytes) {
+      if (h->d_scratch) { CU(cudaDeviceSynchronize()); CU(cudaFree(h->d_scratch)); h->d_scratch = nullptr; h->scratch_bytes = 0; }
+      const size_t want = sl.total + sl.total / 8;
+      CU(cudaMalloc(&h->d_scratch, want));
+      h->scratch_bytes = want;
+    }
+    if (!h->scratch_free) CU(cudaEventCreateWithFlags(&h->scratch_free, cudaEventDisableTiming));
+    if (h->scratch_pending) CU(cudaStreamWaitEvent(stream, h->scratch_free, 0));
+    char* base = static_cast<char*>(h->d_scratch);
+    a.wl_idx = reinterpret_cast<unsigned short*>(base + sl.wl_idx);
+    a.wl_off = reinterpret_cast<int*>(base + sl.wl_off);
+    a.lvlflags = reinterpret_cast<unsigned char*>(base + sl.lvlflags);
+  }
   PostArgs<Real> pa;
   if (post) pa = make_post_args<Real>(post, ncol, in->nlev, post_mask);
-  SideStreams side{{h->side_stream[0], h->side_stream[1]}, h->side_event[0], {h->side_event[1], h->side_event[2]}};
+  SideStreams side;
+  for (int i = 0; i < NUM_SIDE_STREAMS; ++i) { side.stream[i] = h->side_stream[i]; side.join[i] = h->side_event[i + 1]; }
+  side.fork = h->side_event[0];
   const bool use_side = allow_side && h->side_stream[0] && !std::getenv("P3B200_SED_SERIAL");
   h->sed_concurrent = use_side;
   const int rc = launch_main<Real>(a, h->cfg, stream, ev ? reinterpret_cast<void* const*>(ev->m) : nullptr,
-                                   post ? &pa : nullptr, use_side ? &side : nullptr);
+                                   post ? &pa : nullptr, use_side ? &side : nullptr, h->scratch_free);
   if (rc) return cuda_fail((cudaError_t)rc, "p3_main_kernel launch");
+  h->scratch_pending = true;
   return P3B200_OK;
 }
 
@@ -257,11 +283,11 @@ int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p
     if (e != cudaSuccess) rc = cuda_fail(e, "cudaMalloc queue");
   }
   if (rc == P3B200_OK) {
-    for (int i = 0; i < 2 && rc == P3B200_OK; ++i) {
+    for (int i = 0; i < NUM_SIDE_STREAMS && rc == P3B200_OK; ++i) {
       e = cudaStreamCreateWithFlags(&h->side_stream[i], cudaStreamNonBlocking);
       if (e != cudaSuccess) rc = cuda_fail(e, "cudaStreamCreate side");
     }
-    for (int i = 0; i < 3 && rc == P3B200_OK; ++i) {
+    for (int i = 0; i < NUM_SIDE_STREAMS + 1 && rc == P3B200_OK; ++i) {
       e = cudaEventCreateWithFlags(&h->side_event[i], cudaEventDisableTiming);
       if (e != cudaSuccess) rc = cuda_fail(e, "cudaEventCreate side");
     }
@@ -286,6 +312,8 @@ int p3b200_destroy(p3b200_handle h) {
   if (h->d_tables) cudaFree(h->d_tables);
   if (h->d_diag) cudaFree(h->d_diag);
   if (h->d_queue) cudaFree(h->d_queue);
+  if (h->d_scratch) cudaFree(h->d_scratch);
+  if (h->scratch_free) cudaEventDestroy(h->scratch_free);
   if (h->d_budget) cudaFree(h->d_budget);
   if (h->d_checks) cudaFree(h->d_checks);
   delete h;
@@ -639,6 +667,24 @@ int p3b200_last_phase_ms(p3b200_handle h, double* ms6) {
       float t = 0;
       CU(cudaEventElapsedTime(&t, h->events[i].m[from[p]], h->events[i].m[to[p]]));
       ms6[p] += t;
+    }
+  }
+  return P3B200_OK;
+}
+
+int p3b200_last_phase_a_ms(p3b200_handle h, double* ms3) {
+  if (!h || !ms3) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  for (int p = 0; p < 3; ++p) ms3[p] = 0;
+  // marks: 0 start, 7 classification pass done, 8 part2 launches done, 1 column finish done (p3_kernel.cuh)
+  const int from[3] = {0, 7, 8};
+  const int to[3]   = {7, 8, 1};
+  for (size_t i = 0; i < h->events_used; ++i) {
+    CU(cudaEventSynchronize(h->events[i].m[EV_END]));
+    for (int p = 0; p < 3; ++p) {
+      float t = 0;
+      CU(cudaEventElapsedTime(&t, h->events[i].m[from[p]], h->events[i].m[to[p]]));
+      ms3[p] += t;
     }
   }
   return P3B200_OK;

@@ -68,10 +68,15 @@ struct MainArgs {
   int     ncol, nk;
   Real    dt;
   int     predictNc, prescribedCCN, zero_flux_top;
+  int     history_prezeroed;   // the caller zero-filled the three history arrays (what run_impl does before every call)
   Tables<Real>  tb;
   Runtime<Real> ro;
   int*    diag;            // [ncol][D_NUM], always present (the handle owns one if the caller passes none)
-  unsigned int* queue;     // work-queue counters, one per sedimentation launch (species x window class), zeroed before phase A
+  unsigned int* queue;     // work-queue counters: one per sedimentation launch (species x window class) and per part2 group, zeroed before phase A
+  // phase A scratch owned by the handle (p3_abi.cpp), valid between the classification pass and the column finish:
+  unsigned short* wl_idx;  // [ntiles][A_TILE_LEVELS] per tile: tile-local level indices (col_in_tile*nk + k) of the levels part2 has to run on, sorted by class key
+  int*            wl_off;  // [ntiles][8]: start of each process group's segment in the tile's list; [6] = number of entries
+  unsigned char*  lvlflags;// [ncol*nk] per level after part2: LF_* bits (species present, hydrometeors, error bits); 0 on skip_all levels
 };
 
 template <typename Real>
@@ -106,29 +111,25 @@ struct ColAddr {
 //          per-column reductions (hydrometeorsPresent after part2, find_top/find_bottom of the three
 //          sedimenting species) into a small per-column accumulator.
 //
-// The accumulator `acc` is COL_ACC_N ints per column; AT is the access policy (shared-memory atomics in
-// the kernel, plain stores in the host build of this source).
-enum ColAcc { CA_FLAGS = 0, CA_LO_C, CA_HI_C, CA_LO_R, CA_HI_R, CA_LO_I, CA_HI_I, COL_ACC_N };
-enum ColFlag { CF_NUC = 1, CF_HYD1 = 2, CF_HYD2 = 4, CF_ERR_SHIFT = 8 };
-constexpr int A_NKEYS = 32;
-
-struct AccPlain {
-  static P3_HD void or_(int* p, int v) { *p |= v; }
-  static P3_HD void min_(int* p, int v) { if (v < *p) *p = v; }
-  static P3_HD void max_(int* p, int v) { if (v > *p) *p = v; }
-};
+// The two passes are separate kernels (p3_kernel.cu): the classification pass is a streaming kernel at the
+// register budget of a streaming kernel; part2 runs as one launch per PROCESS GROUP (temperature regime x ice
+// present, Phys::part2_level<GRP>) on the class-sorted work lists the classification pass leaves in global memory,
+// each group compiled to the code and registers its regime needs.  What a level reports back to its column
+// (species present after part2 for find_top/find_bottom, hydrometeorsPresent, error bits) is one byte per level
+// (LF_*); a third, tiny kernel folds the bytes of a column into the integer diagnostics.
+enum ColFlag { CF_NUC = 1, CF_HYD1 = 2, CF_ERR_SHIFT = 8 };
+enum LevelFlag { LF_QC = 1, LF_QR = 2, LF_QI = 4, LF_HYD = 8, LF_ERR_SHIFT = 4 };
+constexpr int A_NKEYS = 32;          // sort keys: (tc << 3) | (ice << 2) | (rain << 1) | cloud, tc in {0,1,2}: 24 used
+constexpr int A_NGROUPS = 6;         // process group = key >> 2 = 2*tc + ice (Phys::part2_level<GRP>)
+constexpr int A_OFF_STRIDE = 8;      // ints per tile in MainArgs::wl_off
 
 template <typename Real>
 struct PhaseA {
   using P = Phys<Real>;
   using C = Cst<Real>;
   static P3_HD Real sp(double x) { return static_cast<Real>(x); }
-
-  static P3_HD void acc_init(int* acc) {
-    acc[CA_FLAGS] = 0;
-    acc[CA_LO_C] = MAX_NLEV + 1; acc[CA_HI_C] = -1; acc[CA_LO_R] = MAX_NLEV + 1; acc[CA_HI_R] = -1;
-    acc[CA_LO_I] = MAX_NLEV + 1; acc[CA_HI_I] = -1;
-  }
+  // bit pattern of +0.0 (a -0.0 is stored: only the value the memory already holds may be skipped)
+  static P3_HD bool is_pos_zero(Real x) { return x == 0 && !std::signbit(x); }
 
   // ---- pass 1 -----------------------------------------------------------------------------------
   struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres; };
@@ -218,8 +219,16 @@ struct PhaseA {
     }
     flags |= err << CF_ERR_SHIFT;
     if (!skip_all) {
-      const int tcls = (T <= C::T_rainfrz) ? 2 : (T < Tz) ? 1 : 0;
-      return (int(has_i) << 4) | (int(has_r) << 3) | (int(has_c) << 2) | tcls;
+      // What part2 leaves at its default on most levels is written HERE, with the stores of the neighbouring
+      // skip_all levels (full lines): the three tendencies and the two flux arrays at zero, and the parked
+      // +-T_atm(init).  The part2 launches then store a tendency only where it is non-zero: a lone store into a
+      // line that is not in L2 costs a full-line fill from DRAM.
+      cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = 0; cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = 0; cp.template p<F_NEVAPR>(a)[k] = 0;
+      cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
+      cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = (T < C::T_homogfrz) ? -T0 : T0;
+      // temperature regime of Phys::part2_level<GRP>: 0 T > Tmelt, 1 T_rainfrz < T <= Tmelt, 2 T <= T_rainfrz
+      const int tc = (T <= C::T_rainfrz) ? 2 : (T <= Tz) ? 1 : 0;
+      return (tc << 3) | (int(has_i) << 2) | (int(has_r) << 1) | int(has_c);
     }
     // the level is complete: every hydrometeor was clipped into vapour (p3_main_impl_part1.hpp:123-175),
     // part2 does not run (p3_main_impl.hpp:211-217: its outputs stay zero)
@@ -233,9 +242,10 @@ struct PhaseA {
   }
 
   // ---- pass 2 -----------------------------------------------------------------------------------
-  // `col_active` = nucleationPossible || hydrometeorsPresent of the column (known after pass 1).
-  template <class AT, bool UNI>
-  static P3_HD void pass2_level(const MainArgs<Real>& a, int64_t col, int k, bool col_active, int* acc) {
+  // `col_active` = nucleationPossible || hydrometeorsPresent of the column (known after pass 1).  GRP = the level's
+  // process group (key >> 2) or -1.  Returns the level's LF_* byte.
+  template <bool UNI, int GRP>
+  static P3_HD int pass2_level(const MainArgs<Real>& a, int64_t col, int k, bool col_active) {
     const ColAddr<UNI, Real> cp(a, col);
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
     const Real dt = a.dt, inv_dt = 1 / a.dt;
@@ -300,66 +310,97 @@ struct PhaseA {
     // p3_main_part2 (this level is not skip_all: pass 1 decided that on the same values)
     typename P::Part2Out o;
     const Real* const g_ni_act = a.f[F_NI_ACTIVATED] ? cp.template p<F_NI_ACTIVATED>(a) + k : nullptr;
-    const bool h = P::part2_level(L, a.tb, a.ro, dt, inv_dt, predictNc, prescribedCCN,
-                                  cp.template p<F_QV_PREV>(a) + k, cp.template p<F_T_PREV>(a) + k, g_ni_act, o, err);
-    int fl = (h ? CF_HYD2 : 0) | (err << CF_ERR_SHIFT);
-    if (fl) AT::or_(acc + CA_FLAGS, fl);
-    // find_top / find_bottom (p3_find_impl.hpp) of the sedimenting species on the post-part2 state
-    if (L.qc >= qsmall) { AT::min_(acc + CA_LO_C, k); AT::max_(acc + CA_HI_C, k); }
-    if (L.qr >= qsmall) { AT::min_(acc + CA_LO_R, k); AT::max_(acc + CA_HI_R, k); }
-    if (L.qi >= qsmall) { AT::min_(acc + CA_LO_I, k); AT::max_(acc + CA_HI_I, k); }
+    const bool h = P::template part2_level<GRP>(L, a.tb, a.ro, dt, inv_dt, predictNc, prescribedCCN,
+                                                cp.template p<F_QV_PREV>(a) + k, cp.template p<F_T_PREV>(a) + k, g_ni_act, o, err);
+    // what find_top / find_bottom (p3_find_impl.hpp) and hydrometeorsPresent need from this level
+    const int lf = (L.qc >= qsmall ? LF_QC : 0) | (L.qr >= qsmall ? LF_QR : 0) | (L.qi >= qsmall ? LF_QI : 0) |
+                   (h ? LF_HYD : 0) | (err << LF_ERR_SHIFT);
     *g_qc = L.qc; *g_nc = L.nc; *g_qr = L.qr; *g_nr = L.nr; *g_qi = L.qi;
     *g_qm = L.qm; *g_ni = L.ni; *g_bm = L.bm; *g_qv = L.qv; *g_th = L.th;
-    cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = o.qv2qi_depos_tend;
-    cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = o.precip_total_tend;
-    cp.template p<F_NEVAPR>(a)[k] = o.nevapr;
-    cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
-    cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = frz ? -T0 : T0;
+    // the classification pass wrote zero tendencies, zero fluxes and the parked +-T_atm(init) for this level:
+    // only a tendency whose bit pattern is not +0 needs a store
+    if (!is_pos_zero(o.qv2qi_depos_tend))  cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = o.qv2qi_depos_tend;
+    if (!is_pos_zero(o.precip_total_tend)) cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = o.precip_total_tend;
+    if (!is_pos_zero(o.nevapr))            cp.template p<F_NEVAPR>(a)[k] = o.nevapr;
+    (void)frz;
     // history arrays are only touched where part2 ran (p3_main_impl_part2.hpp:468-470), and part2 only runs
     // for columns that can nucleate or hold hydrometeors after part1 (p3_main_impl.hpp:237); for any other
-    // column all tendencies of this level are exactly zero and the prognostics above are unchanged
+    // column all tendencies of this level are exactly zero and the prognostics above are unchanged.  The caller
+    // zero-fills the three arrays before every call (eamxx_p3_run.cpp:27-29), so a +0 needs no store either.
     if (col_active) {
-      cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = o.liq_ice_exchange;
-      cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = o.vap_liq_exchange;
-      cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = o.vap_ice_exchange;
+      if (!a.history_prezeroed || !is_pos_zero(o.liq_ice_exchange)) cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = o.liq_ice_exchange;
+      if (!a.history_prezeroed || !is_pos_zero(o.vap_liq_exchange)) cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = o.vap_liq_exchange;
+      if (!a.history_prezeroed || !is_pos_zero(o.vap_ice_exchange)) cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = o.vap_ice_exchange;
+    }
+    return lf;
+  }
+
+  // run-time dispatch on the process group (host build; the kernels are instantiated per group)
+  template <bool UNI>
+  static P3_HD int pass2_level_any(const MainArgs<Real>& a, int64_t col, int k, bool col_active, int grp) {
+    switch (grp) {
+      case 0: return pass2_level<UNI, 0>(a, col, k, col_active);
+      case 1: return pass2_level<UNI, 1>(a, col, k, col_active);
+      case 2: return pass2_level<UNI, 2>(a, col, k, col_active);
+      case 3: return pass2_level<UNI, 3>(a, col, k, col_active);
+      case 4: return pass2_level<UNI, 4>(a, col, k, col_active);
+      case 5: return pass2_level<UNI, 5>(a, col, k, col_active);
+      default: return pass2_level<UNI, -1>(a, col, k, col_active);
     }
   }
 
-  // ---- per column, after both passes: flags and sedimentation ranges into the integer diagnostics
-  static P3_HD void finish_column(const MainArgs<Real>& a, int64_t col, const int* acc) {
-    const int fl = acc[CA_FLAGS];
-    const bool nuc = fl & CF_NUC, hyd1 = fl & CF_HYD1, hyd2 = fl & CF_HYD2;
-    const bool active = nuc || hyd1;
-    const bool full = active && hyd2;
+  // ---- per column, after the classification pass: what part1 decided (fl = OR of the levels' pass-1 flags)
+  static P3_HD void column_begin(const MainArgs<Real>& a, int64_t col, int fl) {
     a.f[F_PRECIP_LIQ_SURF][col] = 0;
     a.f[F_PRECIP_ICE_SURF][col] = 0;
     if (a.zero_flux_top) { col_ptr(a, F_PRECIP_LIQ_FLUX, col)[a.nk] = 0; col_ptr(a, F_PRECIP_ICE_FLUX, col)[a.nk] = 0; }
     int* d = a.diag + col * D_NUM;
-    d[D_NUC_POSSIBLE] = nuc; d[D_HYDRO_PART1] = hyd1; d[D_HYDRO_PART2] = active ? (int)hyd2 : -1;
-    const bool c = full && acc[CA_HI_C] >= 0, r = full && acc[CA_HI_R] >= 0, i = full && acc[CA_HI_I] >= 0;
-    d[D_QC_KTOP] = c ? acc[CA_LO_C] : -1; d[D_QC_KBOT] = c ? acc[CA_HI_C] : -1; d[D_QC_NSUB] = 0;
-    d[D_QR_KTOP] = r ? acc[CA_LO_R] : -1; d[D_QR_KBOT] = r ? acc[CA_HI_R] : -1; d[D_QR_NSUB] = 0;
-    d[D_QI_KTOP] = i ? acc[CA_LO_I] : -1; d[D_QI_KBOT] = i ? acc[CA_HI_I] : -1; d[D_QI_NSUB] = 0;
-    d[D_ERROR] = fl >> CF_ERR_SHIFT; d[13] = -1; d[14] = -1; d[15] = -1;
+    d[D_NUC_POSSIBLE] = (fl & CF_NUC) != 0; d[D_HYDRO_PART1] = (fl & CF_HYD1) != 0;
+    d[D_ERROR] = fl >> CF_ERR_SHIFT;
   }
 
-  // Host build only (tests/hostsim): the two passes for one column in the order the kernel runs them.
+  // ---- per column, after part2: hydrometeorsPresent and the sedimentation ranges (find_top / find_bottom,
+  // p3_find_impl.hpp) from the levels' LF_* bytes into the integer diagnostics
+  static P3_HD void column_finish(const MainArgs<Real>& a, int64_t col, const unsigned char* lf) {
+    int* d = a.diag + col * D_NUM;
+    int any = 0, lo_c = MAX_NLEV + 1, hi_c = -1, lo_r = MAX_NLEV + 1, hi_r = -1, lo_i = MAX_NLEV + 1, hi_i = -1;
+    for (int k = 0; k < a.nk; ++k) {
+      const int f = lf[k];
+      any |= f;
+      if (f & LF_QC) { if (k < lo_c) lo_c = k; hi_c = k; }
+      if (f & LF_QR) { if (k < lo_r) lo_r = k; hi_r = k; }
+      if (f & LF_QI) { if (k < lo_i) lo_i = k; hi_i = k; }
+    }
+    const bool active = d[D_NUC_POSSIBLE] || d[D_HYDRO_PART1];
+    const bool hyd2 = (any & LF_HYD) != 0;
+    const bool full = active && hyd2;
+    d[D_HYDRO_PART2] = active ? (int)hyd2 : -1;
+    const bool c = full && hi_c >= 0, r = full && hi_r >= 0, i = full && hi_i >= 0;
+    d[D_QC_KTOP] = c ? lo_c : -1; d[D_QC_KBOT] = c ? hi_c : -1; d[D_QC_NSUB] = 0;
+    d[D_QR_KTOP] = r ? lo_r : -1; d[D_QR_KBOT] = r ? hi_r : -1; d[D_QR_NSUB] = 0;
+    d[D_QI_KTOP] = i ? lo_i : -1; d[D_QI_KBOT] = i ? hi_i : -1; d[D_QI_NSUB] = 0;
+    d[D_ERROR] |= any >> LF_ERR_SHIFT; d[13] = -1; d[14] = -1; d[15] = -1;
+  }
+
+  // Host build only (tests/hostsim): the passes for one column in the order the kernels run them.
   static inline void run_column_host(const MainArgs<Real>& a, int64_t col) {
-    int acc[COL_ACC_N];
-    acc_init(acc);
     int keys[MAX_NLEV];
+    unsigned char lf[MAX_NLEV];
+    int flags = 0;
     for (int k = 0; k < a.nk; ++k) {
       int fl = 0;
       In1 in;
       pass1_load<false>(a, col, k, in);
       keys[k] = pass1_level<false>(a, col, k, in, fl);
-      acc[CA_FLAGS] |= fl;
+      flags |= fl;
+      lf[k] = 0;
     }
-    const bool active = (acc[CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
-    for (int key = A_NKEYS - 1; key >= 0; --key)
+    column_begin(a, col, flags);
+    const bool active = (flags & (CF_NUC | CF_HYD1)) != 0;
+    for (int key = 0; key < A_NKEYS; ++key)
       for (int k = 0; k < a.nk; ++k)
-        if (keys[k] == key) pass2_level<AccPlain, false>(a, col, k, active, acc);
-    finish_column(a, col, acc);
+        if (keys[k] == key) lf[k] = (unsigned char)pass2_level_any<false>(a, col, k, active, key >> 2);
+    column_finish(a, col, lf);
   }
 };
 

@@ -3,10 +3,12 @@
 // Execution model (replaces the Kokkos TeamPolicy of p3_main_impl.hpp:86-113, one team per column, all phases in
 // one kernel separated by team barriers).  p3_main is a short sequence of launches:
 //
-//   p3_phase_a   init + part1 + part2 for one tile of columns per CTA (4 warps).  Pass 1: one thread per level,
-//                coalesced along the column, classifies the level (or finishes it when part2 has nothing to do);
-//                a counting sort by process class in shared memory; pass 2: warps pull groups of 32 same-class
-//                levels and run the fused part1+part2 on them.  Block barriers separate the passes.
+//   p3_classify  init + the deciding part of part1 for one tile of columns per CTA: a streaming pass, one thread per
+//                level, coalesced along the column; finishes the levels part2 has nothing to do on and leaves the
+//                others, counting-sorted by process class, in the tile's work list in global memory.
+//   p3_part2<GRP>  init + part1 + part2 on the listed levels, one launch per process group (temperature regime x ice
+//                present), each compiled to the code and registers its regime needs; persistent warps pull tiles.
+//   p3_column_finish  one thread per column: flags and sedimentation ranges from one byte per level.
 //   p3_sediment<cloud|rain|ice, JW>
 //                CFL sub-stepped sedimentation, one launch per species and window class (JW = 1,2,4,8 register
 //                slots per lane).  One warp per column that holds the species, window of reachable levels in
@@ -57,11 +59,8 @@ struct WarpDev {
 #if !defined(P3B200_A_THREADS)
 #define P3B200_A_THREADS 128
 #endif
-#if !defined(P3B200_A_TILE_LEVELS)
-#define P3B200_A_TILE_LEVELS 4096
-#endif
 #if !defined(P3B200_A_MINB)
-#define P3B200_A_MINB 3
+#define P3B200_A_MINB 6
 #endif
 #if !defined(P3B200_A_P1_UNROLL)
 #define P3B200_A_P1_UNROLL 2
@@ -69,7 +68,6 @@ struct WarpDev {
 constexpr int A_P1_UNROLL = P3B200_A_P1_UNROLL;   // levels per thread in flight in the streaming pass
 constexpr int A_THREADS = P3B200_A_THREADS;
 constexpr int A_MIN_BLOCKS = P3B200_A_MINB;   // resident CTAs per SM the kernel is compiled for (register budget)          // phase A: 4 warps per CTA
-constexpr int A_TILE_LEVELS = P3B200_A_TILE_LEVELS;     // capacity of a CTA's level list (one tile = tile_cols columns x nk levels)
 constexpr int A_MAX_TILE_COLS = 128;
 constexpr int B_WARPS = 4;              // warps per CTA in the sedimentation kernels
 #if !defined(P3B200_C_THREADS)
@@ -80,41 +78,35 @@ constexpr int B_WARPS = 4;              // warps per CTA in the sedimentation ke
 #endif
 constexpr int C_THREADS = P3B200_C_THREADS;
 
-struct AccShared {   // shared-memory accumulator of PhaseA::pass2_level
-  static __device__ __forceinline__ void or_(int* p, int v) { atomicOr(p, v); }
-  static __device__ __forceinline__ void min_(int* p, int v) { atomicMin(p, v); }
-  static __device__ __forceinline__ void max_(int* p, int v) { atomicMax(p, v); }
-};
-
-// Phase A for one tile of `tile_cols` consecutive columns (tile_cols * nk <= A_TILE_LEVELS).
-//   pass 1  thread per level, a warp reads 32 consecutive levels of a column: classify, finish the
-//           skip_all levels, append the others to the tile's list in shared memory (ballot-compacted);
-//   sort    counting sort of the list by key (species present, temperature regime), descending, so
-//           that the expensive classes start first and a warp's 32 lanes take the same branches of part2;
-//   pass 2  warps pull groups of 32 sorted entries from a shared counter and run part1+part2 on them;
-//   finish  one thread per column writes the column's flags and sedimentation ranges.
-template <typename Real, int MINB, bool UNI>
-__global__ void __launch_bounds__(A_THREADS, MINB)
-p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
-  __shared__ unsigned short s_idx[A_TILE_LEVELS];      // pass-1 order: level index inside the tile
+// Phase A, first kernel: the classification pass over one tile of `tile_cols` consecutive columns
+// (tile_cols * nk <= A_TILE_LEVELS).  A streaming kernel: one thread per level, a warp reads 32 consecutive levels of
+// a column (7 coalesced loads, A_P1_UNROLL levels per thread in flight); init + the part of part1 that decides the
+// column flags and the level's skip_all gate.  skip_all levels are complete and stored here; the others are appended
+// to the tile's list in shared memory (ballot-compacted) with their class key, counting-sorted by key and written to
+// the tile's work list in global memory, where the part2 launches find them (one segment per process group).
+template <typename Real, bool UNI>
+__global__ void __launch_bounds__(A_THREADS, A_MIN_BLOCKS)
+p3_classify(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
+  __shared__ unsigned short s_idx[A_TILE_LEVELS];      // pass order: level index inside the tile
   __shared__ unsigned char  s_key[A_TILE_LEVELS];
   __shared__ unsigned short s_sorted[A_TILE_LEVELS];
-  __shared__ int s_acc[A_MAX_TILE_COLS][COL_ACC_N];
+  __shared__ int s_flags[A_MAX_TILE_COLS];
   __shared__ int s_hist[A_NKEYS];
-  __shared__ int s_count, s_next;
+  __shared__ int s_count;
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int nk = a.nk;
   const int64_t col0 = (int64_t)blockIdx.x * tile_cols;
   const int ncols = (int)((a.ncol - col0 < tile_cols) ? (a.ncol - col0) : tile_cols);
   const int nlevels = ncols * nk;
+  unsigned char* const lvl = a.lvlflags + col0 * nk;
 
-  for (int c = tid; c < ncols; c += A_THREADS) PhaseA<Real>::acc_init(s_acc[c]);
+  for (int c = tid; c < ncols; c += A_THREADS) s_flags[c] = 0;
   if (tid < A_NKEYS) s_hist[tid] = 0;
-  if (tid == 0) { s_count = 0; s_next = 0; }
+  if (tid == 0) s_count = 0;
   __syncthreads();
 
-  // ---- pass 1 ---- A_P1_UNROLL levels per thread and iteration: all their loads are in flight before any is consumed
+  // A_P1_UNROLL levels per thread and iteration: all their loads are in flight before any is consumed
   for (int base = tid - lane; base < nlevels; base += A_P1_UNROLL * A_THREADS) {
     int idx[A_P1_UNROLL], c[A_P1_UNROLL], k[A_P1_UNROLL], key[A_P1_UNROLL];
     typename PhaseA<Real>::In1 in[A_P1_UNROLL];
@@ -131,7 +123,8 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
       if (idx[u] < nlevels) {
         int fl = 0;
         key[u] = PhaseA<Real>::template pass1_level<UNI>(a, col0 + c[u], k[u], in[u], fl);
-        if (fl) atomicOr(&s_acc[c[u]][CA_FLAGS], fl);
+        if (fl) atomicOr(&s_flags[c[u]], fl);
+        lvl[idx[u]] = 0;
       }
       const unsigned m = __ballot_sync(0xffffffffu, key[u] >= 0);
       if (m) {
@@ -149,17 +142,22 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
   __syncthreads();
   const int count = s_count;
 
-  // ---- counting sort, descending key; s_hist becomes the running write offset of each key ----
+  // ---- counting sort by key, ascending; s_hist becomes the running write offset of each key; the start of each
+  // process group (4 consecutive keys) goes to the tile's offset table ----
   if (tid < 32) {
-    const int n = s_hist[A_NKEYS - 1 - lane];     // lane 0 holds the largest key
+    const int n = s_hist[lane];
     int incl = n;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int t = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += t;
     }
-    s_hist[A_NKEYS - 1 - lane] = incl - n;
+    s_hist[lane] = incl - n;
+    int* off = a.wl_off + (int64_t)blockIdx.x * A_OFF_STRIDE;
+    if ((lane & 3) == 0 && (lane >> 2) < A_NGROUPS) off[lane >> 2] = incl - n;
+    if (lane == 31) { off[A_NGROUPS] = incl; off[A_NGROUPS + 1] = incl; }
   }
+  for (int c = tid; c < ncols; c += A_THREADS) PhaseA<Real>::column_begin(a, col0 + c, s_flags[c]);
   __syncthreads();
   for (int base = tid - lane; base < count; base += A_THREADS) {
     const int e = base + lane;
@@ -174,25 +172,78 @@ p3_phase_a(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const 
     }
   }
   __syncthreads();
+  unsigned short* const wl = a.wl_idx + (int64_t)blockIdx.x * A_TILE_LEVELS;
+  for (int e = tid; e < count; e += A_THREADS) wl[e] = s_sorted[e];
+}
 
-  // ---- pass 2 ----
-  const int ngroups = (count + 31) >> 5;
-  for (;;) {
-    int g = 0;
-    if (lane == 0) g = atomicAdd(&s_next, 1);
-    g = __shfl_sync(0xffffffffu, g, 0);
-    if (g >= ngroups) break;
-    const int e = g * 32 + lane;
-    if (e < count) {
-      const int idx = s_sorted[e];
+// Phase A, second kernel, one launch per process group GRP (temperature regime x ice present): init + part1 + part2
+// (Phys::part2_level<GRP>) on the levels of the group.  One warp per tile runs the tile's segment of the group in
+// sub-groups of 32 class-sorted levels, so the 32 lanes take the same branches; warps of tiles without levels of the
+// group retire at once.  Each instantiation is compiled to the registers ITS regime needs, and the six launches run
+// side by side on helper streams: the groups that are bound by gather latency (a cold cloud layer one level thick)
+// fill the issue slots the arithmetic-bound ones leave.
+#if !defined(P3B200_P2_THREADS)
+#define P3B200_P2_THREADS 128
+#endif
+constexpr int P2_THREADS = P3B200_P2_THREADS;
+#if !defined(P3B200_P2_MINB_COLD_ICE)
+#define P3B200_P2_MINB_COLD_ICE 3
+#endif
+#if !defined(P3B200_P2_MINB_WARM_ICE)
+#define P3B200_P2_MINB_WARM_ICE 4
+#endif
+#if !defined(P3B200_P2_MINB_NOICE)
+#define P3B200_P2_MINB_NOICE 5
+#endif
+__host__ __device__ constexpr int part2_min_blocks(int grp) {
+  return (grp & 1) == 0 ? P3B200_P2_MINB_NOICE : (grp >> 1) == 0 ? P3B200_P2_MINB_WARM_ICE : P3B200_P2_MINB_COLD_ICE;
+}
+
+template <typename Real, int GRP, bool UNI>
+__global__ void __launch_bounds__(P2_THREADS, part2_min_blocks(GRP))
+p3_part2(const __grid_constant__ MainArgs<Real> a, const int ntiles, const int tile_cols, const unsigned div_magic) {
+  const int lane = threadIdx.x & 31;
+  const int nk = a.nk;
+  const int t = blockIdx.x * (P2_THREADS / 32) + (threadIdx.x >> 5);     // one warp per tile
+  if (t >= ntiles) return;
+  const int* off = a.wl_off + (int64_t)t * A_OFF_STRIDE;
+  const int e0 = __ldg(off + GRP), e1 = __ldg(off + GRP + 1);
+  if (e0 >= e1) return;
+  const unsigned short* wl = a.wl_idx + (int64_t)t * A_TILE_LEVELS;
+  const int64_t col0 = (int64_t)t * tile_cols;
+  for (int base = e0; base < e1; base += 32) {
+    const int e = base + lane;
+    if (e < e1) {
+      const int idx = wl[e];
       const int c = (int)(((unsigned)idx * div_magic) >> 24);
       const int k = idx - c * nk;
-      const bool active = (s_acc[c][CA_FLAGS] & (CF_NUC | CF_HYD1)) != 0;
-      PhaseA<Real>::template pass2_level<AccShared, UNI>(a, col0 + c, k, active, s_acc[c]);
+      const int64_t col = col0 + c;
+      const int* d = a.diag + col * D_NUM;
+      const bool active = (d[D_NUC_POSSIBLE] | d[D_HYDRO_PART1]) != 0;
+      const int lf = PhaseA<Real>::template pass2_level<UNI, GRP>(a, col, k, active);
+      a.lvlflags[col * nk + k] = (unsigned char)lf;
     }
   }
-  __syncthreads();
-  for (int c = tid; c < ncols; c += A_THREADS) PhaseA<Real>::finish_column(a, col0 + c, s_acc[c]);
+}
+
+// Phase A, third kernel: one thread per column folds the levels' LF_* bytes into the integer diagnostics
+// (hydrometeorsPresent after part2, find_top / find_bottom of the three sedimenting species).
+template <typename Real>
+__global__ void __launch_bounds__(128)
+p3_column_finish(const __grid_constant__ MainArgs<Real> a) {
+  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= a.ncol) return;
+  const unsigned char* src = a.lvlflags + col * a.nk;
+  if ((a.nk & 15) == 0) {      // the scratch base is 256-byte aligned: 16-byte loads, all in flight at once
+    __align__(16) unsigned char lf[MAX_NLEV];
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(lf);
+#pragma unroll 4
+    for (int i = 0; i < a.nk / 16; ++i) d4[i] = s4[i];
+    PhaseA<Real>::column_finish(a, col, lf);
+  } else {
+    PhaseA<Real>::column_finish(a, col, src);
+  }
 }
 
 // Sedimentation of species SP for the columns whose window [k_qxtop, nk) needs exactly JW register slots
@@ -349,6 +400,8 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg) {
   if ((rc = plan_species<Real, SP_CLOUD>(sms, need, nk, cfg->b_blocks[0]))) return rc;
   if ((rc = plan_species<Real, SP_RAIN>(sms, need, nk, cfg->b_blocks[1]))) return rc;
   if ((rc = plan_species<Real, SP_ICE>(sms, need, nk, cfg->b_blocks[2]))) return rc;
+  cfg->p2_blocks = (cfg->a_blocks + P2_THREADS / 32 - 1) / (P2_THREADS / 32);   // part2: one warp per tile
+  cfg->fin_blocks = (ncol + 127) / 128;
   const long long levels = (long long)ncol * nk;
   cfg->c_blocks = (int)((levels + C_THREADS - 1) / C_THREADS);
   return 0;
@@ -366,16 +419,38 @@ static void launch_species(const MainArgs<Real>& a, const LaunchConfig& cfg, cud
 
 template <typename Real>
 int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_, void* const* marks, const PostArgs<Real>* post,
-                const SideStreams* side) {
+                const SideStreams* side, void* scratch_free) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a.ncol <= 0) return 0;
   auto mark = [&](int i, cudaStream_t s) { if (marks && marks[i]) cudaEventRecord((cudaEvent_t)marks[i], s); };
   mark(0, stream);
   {
     const bool uni = a.ustride != 0 && a.ustride_flux != 0;
-#define P3_LAUNCH_A(OCC, UNI) p3_phase_a<Real, OCC, UNI><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic)
-    if (uni) P3_LAUNCH_A(A_MIN_BLOCKS, true); else P3_LAUNCH_A(A_MIN_BLOCKS, false);
-#undef P3_LAUNCH_A
+    if (uni) p3_classify<Real, true><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    else     p3_classify<Real, false><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    mark(7, stream);
+#define P3_LAUNCH_P2(G, S) \
+    if (uni) p3_part2<Real, G, true><<<cfg.p2_blocks, P2_THREADS, 0, S>>>(a, cfg.a_blocks, cfg.a_tile_cols, cfg.a_div_magic); \
+    else     p3_part2<Real, G, false><<<cfg.p2_blocks, P2_THREADS, 0, S>>>(a, cfg.a_blocks, cfg.a_tile_cols, cfg.a_div_magic);
+    if (side) {
+      cudaStream_t ss[NUM_SIDE_STREAMS];
+      cudaEventRecord((cudaEvent_t)side->fork, stream);
+      for (int i = 0; i < NUM_SIDE_STREAMS; ++i) {
+        ss[i] = (cudaStream_t)side->stream[i];
+        cudaStreamWaitEvent(ss[i], (cudaEvent_t)side->fork, 0);
+      }
+      P3_LAUNCH_P2(1, stream) P3_LAUNCH_P2(3, ss[0]) P3_LAUNCH_P2(5, ss[1]) P3_LAUNCH_P2(0, ss[2]) P3_LAUNCH_P2(2, ss[3]) P3_LAUNCH_P2(4, ss[4])
+      for (int i = 0; i < NUM_SIDE_STREAMS; ++i) {
+        cudaEventRecord((cudaEvent_t)side->join[i], ss[i]);
+        cudaStreamWaitEvent(stream, (cudaEvent_t)side->join[i], 0);
+      }
+    } else {
+      P3_LAUNCH_P2(5, stream) P3_LAUNCH_P2(3, stream) P3_LAUNCH_P2(1, stream) P3_LAUNCH_P2(4, stream) P3_LAUNCH_P2(2, stream) P3_LAUNCH_P2(0, stream)
+    }
+#undef P3_LAUNCH_P2
+    mark(8, stream);
+    p3_column_finish<Real><<<cfg.fin_blocks, 128, 0, stream>>>(a);
+    if (scratch_free) cudaEventRecord((cudaEvent_t)scratch_free, stream);
   }
   mark(1, stream);
   if (side) {
@@ -420,7 +495,7 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
 
 template int plan_launch<double>(int, int, LaunchConfig*);
 template int plan_launch<float>(int, int, LaunchConfig*);
-template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*, const PostArgs<double>*, const SideStreams*);
-template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*, const PostArgs<float>*, const SideStreams*);
+template int launch_main<double>(const MainArgs<double>&, const LaunchConfig&, void*, void* const*, const PostArgs<double>*, const SideStreams*, void*);
+template int launch_main<float>(const MainArgs<float>&, const LaunchConfig&, void*, void* const*, const PostArgs<float>*, const SideStreams*, void*);
 
 }  // namespace p3b200

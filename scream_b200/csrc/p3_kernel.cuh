@@ -7,11 +7,32 @@
 
 namespace p3b200 {
 
+#if !defined(P3B200_A_TILE_LEVELS)
+#define P3B200_A_TILE_LEVELS 4096
+#endif
+constexpr int A_TILE_LEVELS = P3B200_A_TILE_LEVELS;   // capacity of a tile's level list (one tile = a_tile_cols columns x nk levels)
+
+// Bytes of phase-A scratch p3_main needs for ncol columns of nk levels in tiles of tile_cols columns
+// (MainArgs::wl_idx | wl_off | lvlflags, in this order, each 256-byte aligned).
+struct ScratchLayout { size_t wl_idx, wl_off, lvlflags, total; };
+inline ScratchLayout scratch_layout(int ncol, int nk, int tile_cols) {
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  const size_t ntiles = ((size_t)ncol + tile_cols - 1) / tile_cols;
+  ScratchLayout L;
+  L.wl_idx = 0;
+  L.wl_off = up(ntiles * A_TILE_LEVELS * sizeof(unsigned short));
+  L.lvlflags = L.wl_off + up(ntiles * A_OFF_STRIDE * sizeof(int));
+  L.total = L.lvlflags + up((size_t)ncol * nk + 16);
+  return L;
+}
+
 constexpr int NUM_SED_CLASSES = 4;   // register-window classes of the sedimentation launches: 1, 2, 4, 8 slots per lane
 
 struct LaunchConfig {
   int a_blocks, a_tile_cols;   // phase A: one CTA per tile of a_tile_cols columns
   unsigned a_div_magic;        // (idx * magic) >> 24 == idx / nk inside a tile
+  int p2_blocks;               // part2: one warp per tile, same grid for every process group's launch
+  int fin_blocks;              // column finish: one thread per column
   int b_blocks[3][NUM_SED_CLASSES];   // sedimentation [cloud, rain, ice][JW = 1,2,4,8]: persistent grids (0 = class unused)
   int b_chunk;              // columns per work-queue grab (<= 32)
   int c_blocks;             // phase C: one thread per (column, level)
@@ -25,18 +46,25 @@ int plan_launch(int nk, int ncol, LaunchConfig* cfg);
 // 3*NUM_SED_CLASSES zeroed device counters.  Returns a cudaError_t as int.
 // `marks`: optional NUM_PHASE_MARKS cudaEvent_t: [0] before phase A, [1] after phase A, [2] cloud / [3] rain / [4] ice
 // sedimentation finished, [5] all three joined (phase C may start), [6] after phase C.
-// `side`: optional two helper streams + three events owned by the caller.  The three species share no data except
+// `side`: optional helper streams + events owned by the caller (the six part2 group launches run side by side on
+// them and the caller's stream; sedimentation uses the first two).  The three species share no data except
 // precip_liq_surf (cloud and rain both add into it, atomically; phase A zeroes it): with `side` the ice and cloud
 // launches run on the helper streams beside the rain launches (rain is bound by instruction issue, ice by latency),
 // joined by events before phase C.  Without it the launches are serial on `stream`.
+// `scratch_free`: optional cudaEvent_t recorded when the phase-A scratch (MainArgs::wl_idx/wl_off/lvlflags) is no
+// longer needed by this call.
 // `post`: optional p3_postamble arguments (p3_prepost.cuh); when given, phase C runs the postamble of each
 // (column, level) as its tail and no separate postamble launch is needed.
-constexpr int NUM_PHASE_MARKS = 7;
-struct SideStreams { void* stream[2]; void* fork; void* join[2]; };   // cudaStream_t x2, cudaEvent_t x3
+// [7] after the classification pass, [8] after the part2 launches (inside phase A).
+constexpr int NUM_PHASE_MARKS = 9;
+constexpr int PHASE_MARK_END = 6;
+
+constexpr int NUM_SIDE_STREAMS = 5;
+struct SideStreams { void* stream[NUM_SIDE_STREAMS]; void* fork; void* join[NUM_SIDE_STREAMS]; };   // cudaStream_t, cudaEvent_t
 template <typename Real> struct PostArgs;
 template <typename Real>
 int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, void* const* marks,
-                const PostArgs<Real>* post = nullptr, const SideStreams* side = nullptr);
+                const PostArgs<Real>* post = nullptr, const SideStreams* side = nullptr, void* scratch_free = nullptr);
 
 // Water/energy budget (p3_budget.cu): per-column values into col_vals[ncol][4], fixed-order two-level sum into
 // totals4 (device).  `partials` holds nparts*4 doubles of scratch.  Returns a cudaError_t as int.

@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "p3b200_runtime_defaults", "p3b200_tables_read_text", "p3b200_tables_read_blob",
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
-    "p3b200_last_sed_concurrent",
+    "p3b200_last_sed_concurrent", "p3b200_last_phase_a_ms",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
@@ -100,6 +100,7 @@ def lib(flavour="product"):
                                             ctypes.POINTER(ctypes.c_int64)]
         L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
         L.p3b200_last_sed_concurrent.argtypes = [ctypes.c_void_p]
+        L.p3b200_last_phase_a_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
         L.p3b200_water_energy_totals.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
@@ -374,6 +375,9 @@ class P3Handle:
         check(self._L.p3b200_last_phase_ms(self._h, ms), "p3b200_last_phase_ms")
         out = dict(zip(("phase_a", "sed_cloud", "sed_rain", "sed_ice", "phase_c", "sed_stage"), [float(x) for x in ms]))
         out["sed_concurrent"] = int(self._L.p3b200_last_sed_concurrent(self._h))
+        a3 = (ctypes.c_double * 3)()
+        check(self._L.p3b200_last_phase_a_ms(self._h, a3), "p3b200_last_phase_a_ms")
+        out["a_classify"], out["a_part2"], out["a_finish"] = (float(x) for x in a3)
         return out
 
 
