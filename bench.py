@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--flavour", default="product", choices=["product", "parity"],
                     help="library build: product (ships) or parity (-DP3B200_PARITY, bit-identical to the shared-math oracle)")
+    ap.add_argument("--zero-history", type=int, default=0, choices=[0, 1],
+                    help="P3B200Infra::zero_history: 1 folds run_impl's zero-fill of the three history arrays into the call")
     ap.add_argument("--no-alt", action="store_true", help="skip the second workload line (random-activity IC, G2)")
     ap.add_argument("--alt-steps", type=int, default=5)
     return ap.parse_args()
@@ -254,7 +256,7 @@ def run_b200(args):
 
     handle = p3.P3Handle(local, rb, flavour=args.flavour)
     fstruct, _, _ = handle.fields_struct(fields, host=False)
-    infra = handle._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, True)
+    infra = handle._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, True, zero_history=bool(args.zero_history))
     stream = torch.cuda.current_stream().cuda_stream
 
     def barrier():

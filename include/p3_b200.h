@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define P3B200_ABI_VERSION 1
+#define P3B200_ABI_VERSION 2
 
 /* error codes */
 #define P3B200_OK        0
@@ -126,6 +126,10 @@ typedef struct P3B200Infra {
   int32_t prescribedCCN;
   int32_t zero_flux_top;   /* 1: also zero precip_*_flux[nlev] (what p3_main_f's pre-zeroing achieves,
                               p3_functions_f90.cpp:1941-1945); 0: reference p3_main pack-size-1 behaviour */
+  int32_t zero_history;    /* 1: the call zero-fills liq_ice_exchange / vap_liq_exchange / vap_ice_exchange itself, i.e. it
+                              replaces the caller's zero-fill that precedes every p3_main (eamxx_p3_run.cpp:27-29): the
+                              streaming pass writes the zeros with its other stores and part2 stores non-zero values only.
+                              0: reference p3_main behaviour (the arrays are written where part2 ran, untouched elsewhere) */
 } P3B200Infra;
 
 /* Per-column integer diagnostics (bit-exact parity targets), P3B200_D_NUM int32 per column. */

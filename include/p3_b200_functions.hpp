@@ -260,6 +260,7 @@ struct Functions<ScalarT, B200Device> {
     in.dt = infrastructure.dt; in.it = infrastructure.it; in.ncol = nj; in.nlev = nk;
     in.predictNc = infrastructure.predictNc ? 1 : 0; in.prescribedCCN = infrastructure.prescribedCCN ? 1 : 0;
     in.zero_flux_top = 0;   // reference p3_main with pack size 1 leaves precip_*_flux(nk) to the caller
+    in.zero_history = 0;    // and the history arrays to run_impl's zero-fill (eamxx_p3_run.cpp:27-29)
     int64_t us = 0;
     const int rc = p3b200_main(lookup_tables.handle.get(), &r, &f, &in, stream, &us, nullptr);
     if (rc) fail(rc, "p3_main");

@@ -171,7 +171,7 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
   }
   a.ncol = ncol; a.nk = in->nlev; a.dt = Real(in->dt);
   a.predictNc = in->predictNc; a.prescribedCCN = in->prescribedCCN; a.zero_flux_top = in->zero_flux_top;
-  a.history_prezeroed = 0;   // p3b200_main makes no assumption about the history arrays (run_impl-level callers zero them and say so)
+  a.zero_history = in->zero_history ? 1 : 0;
   if constexpr (sizeof(Real) == 8) a.tb = h->tbd; else a.tb = h->tbf;
   P3B200Runtime r;
   if (runtime) r = *runtime; else runtime_defaults(r);

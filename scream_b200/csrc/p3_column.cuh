@@ -68,7 +68,7 @@ struct MainArgs {
   int     ncol, nk;
   Real    dt;
   int     predictNc, prescribedCCN, zero_flux_top;
-  int     history_prezeroed;   // the caller zero-filled the three history arrays (what run_impl does before every call)
+  int     zero_history;    // P3B200Infra::zero_history: this call zero-fills the three history arrays (the classification pass writes the zeros)
   Tables<Real>  tb;
   Runtime<Real> ro;
   int*    diag;            // [ncol][D_NUM], always present (the handle owns one if the caller passes none)
@@ -174,6 +174,9 @@ struct PhaseA {
   static P3_HD int pass1_level(const MainArgs<Real>& a, int64_t col, int k, const In1& in, int& flags) {
     const ColAddr<UNI, Real> cp(a, col);
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
+    if (a.zero_history) {   // the caller's zero-fill of eamxx_p3_run.cpp:27-29, folded into this pass
+      cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = 0; cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = 0; cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = 0;
+    }
     Real qc = in.qc, qr = in.qr, qi = in.qi, qv = in.qv, th = in.th;
     const Real inv_exner = in.inv_exner;
     // p3_main_init
@@ -325,12 +328,12 @@ struct PhaseA {
     (void)frz;
     // history arrays are only touched where part2 ran (p3_main_impl_part2.hpp:468-470), and part2 only runs
     // for columns that can nucleate or hold hydrometeors after part1 (p3_main_impl.hpp:237); for any other
-    // column all tendencies of this level are exactly zero and the prognostics above are unchanged.  The caller
-    // zero-fills the three arrays before every call (eamxx_p3_run.cpp:27-29), so a +0 needs no store either.
+    // column all tendencies of this level are exactly zero and the prognostics above are unchanged.  With
+    // zero_history the classification pass has zero-filled the three arrays: a +0 needs no store either.
     if (col_active) {
-      if (!a.history_prezeroed || !is_pos_zero(o.liq_ice_exchange)) cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = o.liq_ice_exchange;
-      if (!a.history_prezeroed || !is_pos_zero(o.vap_liq_exchange)) cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = o.vap_liq_exchange;
-      if (!a.history_prezeroed || !is_pos_zero(o.vap_ice_exchange)) cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = o.vap_ice_exchange;
+      if (!a.zero_history || !is_pos_zero(o.liq_ice_exchange)) cp.template p<F_LIQ_ICE_EXCHANGE>(a)[k] = o.liq_ice_exchange;
+      if (!a.zero_history || !is_pos_zero(o.vap_liq_exchange)) cp.template p<F_VAP_LIQ_EXCHANGE>(a)[k] = o.vap_liq_exchange;
+      if (!a.zero_history || !is_pos_zero(o.vap_ice_exchange)) cp.template p<F_VAP_ICE_EXCHANGE>(a)[k] = o.vap_ice_exchange;
     }
     return lf;
   }

@@ -57,7 +57,7 @@ class P3B200Fields(ctypes.Structure):
 class P3B200Infra(ctypes.Structure):
     _fields_ = [("dt", ctypes.c_double), ("it", ctypes.c_int32), ("ncol", ctypes.c_int32),
                 ("nlev", ctypes.c_int32), ("predictNc", ctypes.c_int32), ("prescribedCCN", ctypes.c_int32),
-                ("zero_flux_top", ctypes.c_int32)]
+                ("zero_flux_top", ctypes.c_int32), ("zero_history", ctypes.c_int32)]
 
 
 class P3Error(RuntimeError):
@@ -207,8 +207,9 @@ class P3Handle:
             pass
 
     # ---- argument marshalling ------------------------------------------------------------------
-    def _infra(self, ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, it=1):
-        return P3B200Infra(float(dt), it, ncol, nlev, int(predict_nc), int(prescribed_ccn), int(zero_flux_top))
+    def _infra(self, ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, it=1, zero_history=False):
+        return P3B200Infra(float(dt), it, ncol, nlev, int(predict_nc), int(prescribed_ccn), int(zero_flux_top),
+                           int(zero_history))
 
     def fields_struct(self, fields, host):
         """dict name -> (torch cuda tensor | numpy array), level index contiguous."""
@@ -237,10 +238,10 @@ class P3Handle:
 
     # ---- entry points --------------------------------------------------------------------------
     def main(self, fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None, zero_flux_top=True,
-             stream=None, timed=False, diag=None):
+             stream=None, timed=False, diag=None, zero_history=False):
         """p3_main on device tensors, in place.  Returns device microseconds if timed else None."""
         f, ncol, nlev = self.fields_struct(fields, host=False)
-        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, zero_history=zero_history)
         us = ctypes.c_int64(0)
         sptr = ctypes.c_void_p(stream) if stream else None
         dptr = ctypes.c_void_p(diag.data_ptr()) if diag is not None else None

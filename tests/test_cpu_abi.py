@@ -32,7 +32,7 @@ def test_header_symbols_exported(p3lib):
 
 def test_abi_version_and_strerror(p3lib):
     L = p3lib.lib()
-    assert L.p3b200_abi_version() == 1
+    assert L.p3b200_abi_version() == 2
     for code in (0, -1, -2, -3, -4, -5):
         assert L.p3b200_strerror(code)
     assert b"CUDA" in L.p3b200_strerror(-2).upper()

@@ -172,3 +172,29 @@ def test_runtime_knobs_generic_rain_table_path(oracle, handle64, p3lib):
     errs = parity.field_errors(ref, got)
     assert not _report(errs, parity.TOL[8]), _report(errs, parity.TOL[8])
     assert np.array_equal(d_ref, handle64.get_diag(3))
+
+
+@pytest.mark.parametrize("rb", [8, 4])
+def test_zero_history_replaces_the_callers_zero_fill(p3lib, rb):
+    """P3B200Infra::zero_history = 1 on arrays full of garbage == the caller's zero-fill (eamxx_p3_run.cpp:27-29)
+    followed by the reference-shaped call, bit for bit, on every output."""
+    import torch
+    h = p3lib.P3Handle(0, rb)
+    f = ic_cases.make_random(1024, 128, seed=7)
+    if rb == 4:
+        f = {k: v.astype(np.float32) for k, v in f.items()}
+    a = parity.clone(f)
+    parity.zero_outputs(a)
+    da = p3lib.to_device(a)
+    h.main(da, 300.0, True, True)
+    ra = p3lib.to_host(da)
+    b = parity.clone(f)
+    parity.zero_outputs(b)
+    for n in parity.HISTORY:
+        b[n][...] = 12345.0
+    db = p3lib.to_device(b)
+    h.main(db, 300.0, True, True, zero_history=True)
+    rbk = p3lib.to_host(db)
+    for n in OUTPUTS:
+        assert np.array_equal(ra[n], rbk[n], equal_nan=True), n
+    h.close()
