@@ -214,6 +214,40 @@ int p3b200_last_sed_concurrent(p3b200_handle h);
 int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
                                void* cuda_stream, double* totals4_dev, double* totals4_host);
 
+/* ---- the column conservation check the atmosphere driver wraps around a process --------------------------
+ * MassAndEnergyColumnConservationCheck (share/property_checks/mass_and_energy_column_conservation_check.cpp): before
+ * the process runs the driver stores each column's total water mass and total energy (compute_current_mass / _energy,
+ * :56-107); after it, check() (:110-215) forms the relative error of both against the stored value plus the boundary
+ * fluxes the process reported (vapor/water/ice/heat flux, written by the postamble) times dt, and reduces each with
+ * Kokkos::MaxLoc over the columns.  Pass when both maxima are below their tolerance.
+ *   mass   = sum_k (qv+qc+qi+qr)*pseudo_density/g
+ *   energy = sum_k (T_mid*Cpair + 0.5*(u^2+v^2) + (LatVap+LatIce)*qv + LatIce*(qc+qr))*pseudo_density/g + phis*ps/g
+ * The within-column sums run in level order (the reference serialises them under ekatBFB), so the values have the bits
+ * of the sequential sum.  Device pointers; 2-D fields (ncol, nlev) with `col_stride`; horiz_winds is (ncol, 2, nlev):
+ * component c of column i starts at horiz_winds + i*wind_col_stride + c*wind_comp_stride.  Per-column arrays: ncol.
+ * _begin stores the before-values in the handle; _check compares.  A NaN error never wins the MaxLoc (`err > max`),
+ * equal errors report the lowest column; *_col is -1 when no column's error exceeded the reduction identity. */
+typedef struct P3B200ConservationFields {
+  const void *pseudo_density, *T_mid, *horiz_winds, *qv, *qc, *qi, *qr;
+  const void *ps, *phis;                                       /* [ncol] */
+  const void *vapor_flux, *water_flux, *ice_flux, *heat_flux;  /* [ncol]; only read by _check */
+  int64_t col_stride, wind_col_stride, wind_comp_stride;
+} P3B200ConservationFields;
+typedef struct P3B200ConservationResult {
+  double mass_rel_err, energy_rel_err;     /* the two maxima */
+  int64_t mass_col, energy_col;            /* local column index of each */
+  int32_t pass;                            /* 1: both below tolerance */
+  int32_t mass_below_tol, energy_below_tol, reserved;
+} P3B200ConservationResult;
+int p3b200_column_conservation_begin(p3b200_handle h, const P3B200ConservationFields* f, int32_t ncol, int32_t nlev,
+                                     void* cuda_stream);
+int p3b200_column_conservation_check(p3b200_handle h, const P3B200ConservationFields* f, int32_t ncol, int32_t nlev,
+                                     double dt, double mass_error_tolerance, double energy_error_tolerance,
+                                     P3B200ConservationResult* result, void* cuda_stream);
+/* the stored before-values and the per-column relative errors of the last _check (device -> host copies; NULL skips) */
+int p3b200_column_conservation_get(p3b200_handle h, int32_t ncol, double* mass, double* energy, double* rel_mass,
+                                   double* rel_energy);
+
 /* ---- P3Microphysics::run_impl brackets p3_main with p3_preamble / p3_postamble ------------------------
  * (eamxx_p3_run.cpp:11-16, 39-44; functors eamxx_p3_process_interface.hpp:62-195, 200-262; the helper formulas
  * are share/util/scream_common_physics_functions_impl.hpp:88-97, 115-118, 162-165, 214-222, 327-331, 375-379,

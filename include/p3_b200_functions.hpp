@@ -196,12 +196,13 @@ struct Functions<ScalarT, B200Device> {
   // Static method p3_main (p3_functions.hpp:1356-1369; p3_main_impl.hpp:335-372): same argument list,
   // returns the device time of the call in microseconds.  Views hold DEVICE pointers.  `stream` is an
   // optional cudaStream_t; like the reference (Kokkos::fence, p3_main_impl.hpp:326) the call returns
-  // after the work has completed.
+  // after the work has completed.  `zero_history` (an extension): the call zero-fills the three history arrays
+  // itself, replacing the three deep_copy(0.0) that precede p3_main in run_impl.
   static Int p3_main(const P3Runtime& runtime, const P3PrognosticState& prognostic_state,
                      const P3DiagnosticInputs& diagnostic_inputs, const P3DiagnosticOutputs& diagnostic_outputs,
                      const P3Infrastructure& infrastructure, const P3HistoryOnly& history_only,
                      const P3LookupTables& lookup_tables, const WorkspaceManager& /*workspace_mgr*/,
-                     Int nj, Int nk, void* stream = nullptr) {
+                     Int nj, Int nk, void* stream = nullptr, bool zero_history = false) {
     if (!lookup_tables.handle) fail(P3B200_EINVAL, "p3_main: lookup tables not initialised (p3_init)");
     P3B200Fields f;
     for (int i = 0; i < P3B200_F_NUM; ++i) { f.ptr[i] = nullptr; f.col_stride[i] = 0; }
@@ -260,7 +261,8 @@ struct Functions<ScalarT, B200Device> {
     in.dt = infrastructure.dt; in.it = infrastructure.it; in.ncol = nj; in.nlev = nk;
     in.predictNc = infrastructure.predictNc ? 1 : 0; in.prescribedCCN = infrastructure.prescribedCCN ? 1 : 0;
     in.zero_flux_top = 0;   // reference p3_main with pack size 1 leaves precip_*_flux(nk) to the caller
-    in.zero_history = 0;    // and the history arrays to run_impl's zero-fill (eamxx_p3_run.cpp:27-29)
+    // the history arrays are left to run_impl's zero-fill (eamxx_p3_run.cpp:27-29) unless the caller folds it in
+    in.zero_history = zero_history ? 1 : 0;
     int64_t us = 0;
     const int rc = p3b200_main(lookup_tables.handle.get(), &r, &f, &in, stream, &us, nullptr);
     if (rc) fail(rc, "p3_main");

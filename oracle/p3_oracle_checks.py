@@ -70,3 +70,60 @@ def repair(v, lb, ub):
 def p3_checks(fields, checks):
     """fields: {name: array}; checks: scream_b200.fields.CHECKS -> {name: check dict}"""
     return {name: check(fields[name], lb, ub, rep) for name, lb, ub, rep in checks}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# MassAndEnergyColumnConservationCheck  share/property_checks/mass_and_energy_column_conservation_check.cpp
+#   compute_total_mass_on_column :283-301, compute_mass_boundary_flux_on_column :304-312,
+#   compute_total_energy_on_column :314-347, compute_energy_boundary_flux_on_column :349-363, check() :110-215.
+# Constants: physics/share/physics_constants.hpp (gravit 9.80616, Cpair 1004.64, LatVap 2501000, LatIce 333700,
+# RHO_H2O 1000).  The within-column sums run level by level in index order (the reference serialises them under
+# ekatBFB); everything is evaluated in the precision of the fields, as the reference does with Real.
+GRAVIT, CPAIR, LATVAP, LATICE, RHO_H2O = 9.80616, 1004.64, 2501000.0, 333700.0, 1000.0
+
+
+def _seq_sum(terms):
+    acc = np.zeros(terms.shape[0], dtype=terms.dtype)
+    for k in range(terms.shape[1]):
+        acc = acc + terms[:, k]
+    return acc
+
+
+def column_mass(f):
+    t = f["qv"].dtype.type
+    terms = (f["qv"] + f["qc"] + f["qi"] + f["qr"]) * f["pseudo_density"] / t(GRAVIT)
+    return _seq_sum(terms)
+
+
+def column_energy(f):
+    t = f["qv"].dtype.type
+    u, v = f["horiz_winds"][:, 0, :], f["horiz_winds"][:, 1, :]
+    u2, v2 = u * u, v * v
+    terms = (f["T_mid"] * t(CPAIR) + t(0.5) * (u2 + v2) + (t(LATVAP) + t(LATICE)) * f["qv"] +
+             t(LATICE) * (f["qc"] + f["qr"])) * f["pseudo_density"] / t(GRAVIT)
+    return _seq_sum(terms) + f["phis"] * f["ps"] / t(GRAVIT)
+
+
+def column_conservation_check(f, prev_mass, prev_energy, dt, mass_tol, energy_tol):
+    """check(): returns dict(mass_rel_err, mass_col, energy_rel_err, energy_col, pass_) + the per-column errors."""
+    t = f["qv"].dtype.type
+    dt = t(dt)
+    tm, te = column_mass(f), column_energy(f)
+    tm_exp = prev_mass + (f["vapor_flux"] - f["water_flux"] * t(RHO_H2O)) * dt
+    te_exp = prev_energy + (f["vapor_flux"] * (t(LATVAP) + t(LATICE)) -
+                            (f["water_flux"] - f["ice_flux"]) * t(RHO_H2O) * t(LATICE) + f["heat_flux"]) * dt
+    with np.errstate(divide="ignore", invalid="ignore"):
+        rel_m = np.abs(tm - tm_exp) / prev_mass
+        rel_e = np.abs(te - te_exp) / prev_energy
+
+    def maxloc(v):   # Kokkos::MaxLoc identity, `v > best` updates: NaN never wins, first (lowest) column on ties
+        best, loc = -float(np.finfo(v.dtype).max), -1
+        for i, x in enumerate(v):
+            if x > best:
+                best, loc = float(x), i
+        return best, loc
+
+    mv, ml = maxloc(rel_m)
+    ev, el = maxloc(rel_e)
+    return {"mass_rel_err": mv, "mass_col": ml, "energy_rel_err": ev, "energy_col": el,
+            "pass_": bool(mv < mass_tol and ev < energy_tol), "rel_mass": rel_m, "rel_energy": rel_e}

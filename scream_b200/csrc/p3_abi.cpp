@@ -80,6 +80,8 @@ struct p3b200_ctx {
   LaunchConfig cfg{};
   int cfg_nk = -1, cfg_ncol = -1;
   unsigned long long* d_checks = nullptr;   // 2*CHK_NUM min/max keys + 2 location slots (property checks)
+  double* d_cons = nullptr;       // column conservation check: mass | energy | rel_mass | rel_energy [cons_cols] + 4 results
+  size_t cons_cols = 0;
   double* d_budget = nullptr;     // [budget_cols][4] per-column values + BUDGET_PARTS*4 partials + 4 totals
   size_t budget_cols = 0;
   // helper streams/events that let the three sedimentation species run side by side (p3_kernel.cuh: SideStreams)
@@ -315,6 +317,7 @@ int p3b200_destroy(p3b200_handle h) {
   if (h->d_scratch) cudaFree(h->d_scratch);
   if (h->scratch_free) cudaEventDestroy(h->scratch_free);
   if (h->d_budget) cudaFree(h->d_budget);
+  if (h->d_cons) cudaFree(h->d_cons);
   if (h->d_checks) cudaFree(h->d_checks);
   delete h;
   return P3B200_OK;
@@ -669,6 +672,82 @@ int p3b200_last_phase_ms(p3b200_handle h, double* ms6) {
       ms6[p] += t;
     }
   }
+  return P3B200_OK;
+}
+
+}  // extern "C"
+namespace {
+template <typename Real>
+ConsArgs<Real> make_cons_args(const P3B200ConservationFields* f, int ncol, int nlev, double dt) {
+  ConsArgs<Real> a;
+  auto p = [](const void* v) { return static_cast<const Real*>(v); };
+  a.pseudo_density = p(f->pseudo_density); a.T_mid = p(f->T_mid); a.horiz_winds = p(f->horiz_winds);
+  a.qv = p(f->qv); a.qc = p(f->qc); a.qi = p(f->qi); a.qr = p(f->qr); a.ps = p(f->ps); a.phis = p(f->phis);
+  a.vapor_flux = p(f->vapor_flux); a.water_flux = p(f->water_flux); a.ice_flux = p(f->ice_flux); a.heat_flux = p(f->heat_flux);
+  a.col_stride = f->col_stride ? f->col_stride : nlev;
+  a.wind_comp_stride = f->wind_comp_stride ? f->wind_comp_stride : nlev;
+  a.wind_col_stride = f->wind_col_stride ? f->wind_col_stride : 2 * (int64_t)nlev;
+  a.ncol = ncol; a.nk = nlev; a.dt = Real(dt);
+  return a;
+}
+int cons_run(p3b200_ctx* h, const P3B200ConservationFields* f, int ncol, int nlev, double dt, bool check, void* stream) {
+  if (!f || ncol < 0 || nlev < 1) return P3B200_EINVAL;
+  if (!f->pseudo_density || !f->T_mid || !f->horiz_winds || !f->qv || !f->qc || !f->qi || !f->qr || !f->ps || !f->phis)
+    return P3B200_EINVAL;
+  if (check && (!f->vapor_flux || !f->water_flux || !f->ice_flux || !f->heat_flux)) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  if (check && (h->cons_cols < (size_t)ncol || !h->d_cons)) return P3B200_EINVAL;    // no matching _begin
+  if (h->cons_cols < (size_t)ncol || !h->d_cons) {
+    if (h->d_cons) { CU(cudaDeviceSynchronize()); CU(cudaFree(h->d_cons)); h->d_cons = nullptr; }
+    CU(cudaMalloc(&h->d_cons, ((size_t)ncol * 4 + 4) * sizeof(double)));
+    h->cons_cols = (size_t)ncol;
+  }
+  double* base = h->d_cons;
+  const size_t n = h->cons_cols;
+  const int rc = h->real_bytes == 8
+      ? launch_conservation<double>(make_cons_args<double>(f, ncol, nlev, dt), check, base, base + n, base + 2 * n, base + 3 * n, base + 4 * n, stream)
+      : launch_conservation<float>(make_cons_args<float>(f, ncol, nlev, dt), check, base, base + n, base + 2 * n, base + 3 * n, base + 4 * n, stream);
+  if (rc) return cuda_fail((cudaError_t)rc, "p3_column_conservation launch");
+  return P3B200_OK;
+}
+}  // namespace
+extern "C" {
+
+int p3b200_column_conservation_begin(p3b200_handle h, const P3B200ConservationFields* f, int32_t ncol, int32_t nlev,
+                                     void* cuda_stream) {
+  if (!h) return P3B200_EINVAL;
+  return cons_run(h, f, ncol, nlev, 0.0, false, cuda_stream);
+}
+
+int p3b200_column_conservation_check(p3b200_handle h, const P3B200ConservationFields* f, int32_t ncol, int32_t nlev,
+                                     double dt, double mass_tol, double energy_tol, P3B200ConservationResult* result,
+                                     void* cuda_stream) {
+  if (!h || !result || !(dt == dt)) return P3B200_EINVAL;    // the reference requires dt to be set (:118-119)
+  const int rc = cons_run(h, f, ncol, nlev, dt, true, cuda_stream);
+  if (rc) return rc;
+  double out[4] = {0, -1, 0, -1};
+  if (ncol > 0) {
+    CU(cudaMemcpyAsync(out, h->d_cons + 4 * h->cons_cols, sizeof(out), cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    CU(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+  } else {
+    out[0] = out[2] = h->real_bytes == 4 ? -(double)FLT_MAX : -DBL_MAX;
+  }
+  result->mass_rel_err = out[0]; result->mass_col = (int64_t)out[1];
+  result->energy_rel_err = out[2]; result->energy_col = (int64_t)out[3];
+  result->mass_below_tol = out[0] < mass_tol; result->energy_below_tol = out[2] < energy_tol;     // :202-203
+  result->pass = result->mass_below_tol && result->energy_below_tol;
+  result->reserved = 0;
+  return P3B200_OK;
+}
+
+int p3b200_column_conservation_get(p3b200_handle h, int32_t ncol, double* mass, double* energy, double* rel_mass,
+                                   double* rel_energy) {
+  if (!h || ncol < 0 || (size_t)ncol > h->cons_cols || !h->d_cons) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  double* dst[4] = {mass, energy, rel_mass, rel_energy};
+  for (int i = 0; i < 4; ++i)
+    if (dst[i]) CU(cudaMemcpy(dst[i], h->d_cons + (size_t)i * h->cons_cols, (size_t)ncol * sizeof(double), cudaMemcpyDeviceToHost));
   return P3B200_OK;
 }
 

@@ -94,6 +94,107 @@ int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, i
   return (int)cudaGetLastError();
 }
 
+// =================================================================================================
+// MassAndEnergyColumnConservationCheck (share/property_checks/mass_and_energy_column_conservation_check.cpp): the
+// atmosphere driver calls compute_current_mass / compute_current_energy before a process runs (:56-107) and check()
+// after it (:110-215).  Per column, with the within-column sums formed level by level in index order (the reference
+// serialises them under ekatBFB, ekat_kokkos_utils.hpp:248):
+//   mass   = sum_k (qv+qc+qi+qr) * pseudo_density / g                                                    (:283-301)
+//   energy = sum_k (T*Cpair + 0.5*(u^2+v^2) + (LatVap+LatIce)*qv + LatIce*(qc+qr)) * pseudo_density / g + phis*ps/g   (:314-347)
+//   check: rel_err_mass   = |mass - (mass_prev + (vapor_flux - water_flux*RHO_H2O)*dt)| / mass_prev       (:157-170)
+//          rel_err_energy = |energy - (energy_prev + (vapor_flux*(LatVap+LatIce) - (water_flux-ice_flux)*RHO_H2O*LatIce
+//                                                    + heat_flux)*dt)| / energy_prev                      (:185-199)
+//   and the MaxLoc of each over the columns (`rel_err > result.val`: NaN never wins; ties: lowest column).
+// One warp per column: the 32 lanes evaluate 32 levels' terms from coalesced loads, lane 0 adds them in level order
+// (one shuffle per level), so the result has the bits of the sequential sum.
+template <typename Real, bool CHECK>
+__global__ void __launch_bounds__(BUD_WARPS * 32)
+p3_column_conservation(const ConsArgs<Real> a, double* __restrict__ mass, double* __restrict__ energy,
+                       double* __restrict__ rel_mass, double* __restrict__ rel_energy) {
+  const int lane = threadIdx.x & 31;
+  const int64_t col = (int64_t)blockIdx.x * BUD_WARPS + (threadIdx.x >> 5);
+  if (col >= a.ncol) return;
+  using C = Cst<Real>;
+  const int64_t o = col * a.col_stride;
+  const Real* u = a.horiz_winds + col * a.wind_col_stride;
+  const Real* v = u + a.wind_comp_stride;
+  Real tm = 0, te = 0;
+  for (int k0 = 0; k0 < a.nk; k0 += 32) {
+    const int k = k0 + lane;
+    Real m_term = 0, e_term = 0;
+    if (k < a.nk) {
+      const Real qv = a.qv[o + k], qc = a.qc[o + k], qi = a.qi[o + k], qr = a.qr[o + k], pd = a.pseudo_density[o + k];
+      m_term = (qv + qc + qi + qr) * pd / C::gravit;
+      const Real u2 = u[k] * u[k], v2 = v[k] * v[k];
+      e_term = (a.T_mid[o + k] * C::Cpair + Real(0.5) * (u2 + v2) + (C::LatVap + C::LatIce) * qv + C::LatIce * (qc + qr)) * pd / C::gravit;
+    }
+    const int n = (a.nk - k0 < 32) ? a.nk - k0 : 32;
+    for (int j = 0; j < n; ++j) {
+      tm += __shfl_sync(0xffffffffu, m_term, j);
+      te += __shfl_sync(0xffffffffu, e_term, j);
+    }
+  }
+  if (lane != 0) return;
+  te += a.phis[col] * a.ps[col] / C::gravit;
+  if (!CHECK) { mass[col] = (double)tm; energy[col] = (double)te; return; }
+  const Real dt = a.dt;
+  const Real prev_m = (Real)mass[col], prev_e = (Real)energy[col];
+  const Real vf = a.vapor_flux[col], wf = a.water_flux[col], icf = a.ice_flux[col], hf = a.heat_flux[col];
+  const Real tm_exp = prev_m + (vf - wf * C::RHO_H2O) * dt;
+  const Real te_exp = prev_e + (vf * (C::LatVap + C::LatIce) - (wf - icf) * C::RHO_H2O * C::LatIce + hf) * dt;
+  rel_mass[col] = (double)(std::abs(tm - tm_exp) / prev_m);
+  rel_energy[col] = (double)(std::abs(te - te_exp) / prev_e);
+}
+
+// MaxLoc over the columns for both error arrays: out[0] = max mass error, out[1] = its column, out[2], out[3] energy.
+// Starts from the reduction identity (lowest finite value, column -1); `v > best` as in the reference.
+__global__ void __launch_bounds__(1024)
+p3_conservation_maxloc(const double* __restrict__ rel_mass, const double* __restrict__ rel_energy, int64_t ncol,
+                       double* __restrict__ out4, int real_bytes) {
+  __shared__ double sv[2][1024];
+  __shared__ long long si[2][1024];
+  const double ident = real_bytes == 4 ? -(double)3.402823466e+38f : -1.7976931348623157e+308;
+  double best[2] = {ident, ident};
+  long long loc[2] = {-1, -1};
+  for (int64_t i = threadIdx.x; i < ncol; i += 1024) {
+    const double m = rel_mass[i], e = rel_energy[i];
+    if (m > best[0]) { best[0] = m; loc[0] = i; }
+    if (e > best[1]) { best[1] = e; loc[1] = i; }
+  }
+  for (int w = 0; w < 2; ++w) { sv[w][threadIdx.x] = best[w]; si[w][threadIdx.x] = loc[w]; }
+  __syncthreads();
+  for (int h = 512; h > 0; h >>= 1) {
+    if ((int)threadIdx.x < h)
+      for (int w = 0; w < 2; ++w) {
+        const double ov = sv[w][threadIdx.x + h];
+        const long long oi = si[w][threadIdx.x + h];
+        const double mv = sv[w][threadIdx.x];
+        const long long mi = si[w][threadIdx.x];
+        // larger value wins; on equal values the lower column (what a serial sweep reports)
+        if (ov > mv || (ov == mv && oi >= 0 && (mi < 0 || oi < mi))) { sv[w][threadIdx.x] = ov; si[w][threadIdx.x] = oi; }
+      }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out4[0] = sv[0][0]; out4[1] = (double)si[0][0]; out4[2] = sv[1][0]; out4[3] = (double)si[1][0]; }
+}
+
+template <typename Real>
+int launch_conservation(const ConsArgs<Real>& a, bool check, double* mass, double* energy, double* rel_mass,
+                        double* rel_energy, double* out4, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (a.ncol <= 0) return 0;
+  const int blocks = (a.ncol + BUD_WARPS - 1) / BUD_WARPS;
+  if (!check) {
+    p3_column_conservation<Real, false><<<blocks, BUD_WARPS * 32, 0, stream>>>(a, mass, energy, rel_mass, rel_energy);
+  } else {
+    p3_column_conservation<Real, true><<<blocks, BUD_WARPS * 32, 0, stream>>>(a, mass, energy, rel_mass, rel_energy);
+    p3_conservation_maxloc<<<1, 1024, 0, stream>>>(rel_mass, rel_energy, a.ncol, out4, (int)sizeof(Real));
+  }
+  return (int)cudaGetLastError();
+}
+template int launch_conservation<double>(const ConsArgs<double>&, bool, double*, double*, double*, double*, double*, void*);
+template int launch_conservation<float>(const ConsArgs<float>&, bool, double*, double*, double*, double*, double*, void*);
+
 template int launch_budget<double>(const MainArgs<double>&, double*, double*, int, double*, void*);
 template int launch_budget<float>(const MainArgs<float>&, double*, double*, int, double*, void*);
 

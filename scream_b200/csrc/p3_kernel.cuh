@@ -72,6 +72,21 @@ constexpr int BUDGET_PARTS = 256;
 template <typename Real>
 int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, int nparts, double* totals4, void* stream);
 
+// MassAndEnergyColumnConservationCheck (p3_budget.cu).  check = false: compute_current_mass / compute_current_energy
+// into mass[ncol] / energy[ncol]; check = true: relative errors per column into rel_mass / rel_energy and their MaxLoc
+// into out4 = {max mass error, column, max energy error, column}.
+template <typename Real>
+struct ConsArgs {
+  const Real *pseudo_density, *T_mid, *horiz_winds, *qv, *qc, *qi, *qr, *ps, *phis;
+  const Real *vapor_flux, *water_flux, *ice_flux, *heat_flux;
+  int64_t col_stride, wind_col_stride, wind_comp_stride;
+  int ncol, nk;
+  Real dt;
+};
+template <typename Real>
+int launch_conservation(const ConsArgs<Real>& a, bool check, double* mass, double* energy, double* rel_mass,
+                        double* rel_energy, double* out4, void* stream);
+
 }  // namespace p3b200
 
 // p3_prepost.cu: p3_preamble / p3_postamble launches from the C-ABI structs.  Return a cudaError_t as int.

@@ -83,3 +83,8 @@ CHECK_COLUMN_FIELDS = ("precip_liq_surf_mass", "precip_ice_surf_mass")
 CHECK_POSTAMBLE_SOURCE = {"T_mid": "T_atm", "eff_radius_qc": "diag_eff_radius_qc", "eff_radius_qi": "diag_eff_radius_qi",
                           "eff_radius_qr": "diag_eff_radius_qr"}
 CHECK_PASS, CHECK_REPAIRABLE, CHECK_FAIL = 0, 1, 2
+
+# MassAndEnergyColumnConservationCheck (share/property_checks/mass_and_energy_column_conservation_check.cpp):
+# pointer members of P3B200ConservationFields in declaration order
+CONSERVATION_FIELDS = ("pseudo_density", "T_mid", "horiz_winds", "qv", "qc", "qi", "qr", "ps", "phis",
+                       "vapor_flux", "water_flux", "ice_flux", "heat_flux")

@@ -10,7 +10,7 @@ import subprocess
 
 import numpy as np
 
-from .fields import (CHECK_COLUMN_FIELDS, CHECK_FIELDS, FIELDS, INTERFACE_FIELDS, NUM_DIAG, POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D, PREAMBLE_FIELDS,
+from .fields import (CONSERVATION_FIELDS, CHECK_COLUMN_FIELDS, CHECK_FIELDS, FIELDS, INTERFACE_FIELDS, NUM_DIAG, POSTAMBLE_FIELDS_1D, POSTAMBLE_FIELDS_2D, PREAMBLE_FIELDS,
                      RUNTIME_DEFAULTS, SURFACE_1D)
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
@@ -29,6 +29,7 @@ ABI_SYMBOLS = [
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
     "p3b200_last_sed_concurrent", "p3b200_last_phase_a_ms",
+    "p3b200_column_conservation_begin", "p3b200_column_conservation_check", "p3b200_column_conservation_get",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
@@ -101,6 +102,11 @@ def lib(flavour="product"):
         L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
         L.p3b200_last_sed_concurrent.argtypes = [ctypes.c_void_p]
         L.p3b200_last_phase_a_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
+        L.p3b200_column_conservation_begin.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.p3b200_column_conservation_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
+                                                       ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p,
+                                                       ctypes.c_void_p]
+        L.p3b200_column_conservation_get.argtypes = [ctypes.c_void_p, ctypes.c_int32] + [ctypes.c_void_p] * 4
         L.p3b200_water_energy_totals.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
@@ -161,6 +167,17 @@ class P3B200CheckResult(ctypes.Structure):
     _fields_ = [("lb", ctypes.c_double), ("ub", ctypes.c_double), ("min_val", ctypes.c_double), ("max_val", ctypes.c_double),
                 ("min_loc", ctypes.c_int64), ("max_loc", ctypes.c_int64), ("result", ctypes.c_int32),
                 ("pass_lower", ctypes.c_int32), ("pass_upper", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+class P3B200ConservationFields(ctypes.Structure):
+    _fields_ = ([(n, ctypes.c_void_p) for n in CONSERVATION_FIELDS] +
+                [("col_stride", ctypes.c_int64), ("wind_col_stride", ctypes.c_int64), ("wind_comp_stride", ctypes.c_int64)])
+
+
+class P3B200ConservationResult(ctypes.Structure):
+    _fields_ = [("mass_rel_err", ctypes.c_double), ("energy_rel_err", ctypes.c_double), ("mass_col", ctypes.c_int64),
+                ("energy_col", ctypes.c_int64), ("pass_", ctypes.c_int32), ("mass_below_tol", ctypes.c_int32),
+                ("energy_below_tol", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 def _check_results(arr):
@@ -352,6 +369,37 @@ class P3Handle:
         ncol, nlev = qv.shape
         check(self._L.p3b200_repair_qv(self._h, ctypes.c_void_p(qv.data_ptr()), ctypes.c_int64(qv.stride(0)), ncol, nlev,
                                      ctypes.c_void_p(stream or 0)), "p3b200_repair_qv")
+
+    def _conservation_struct(self, fields):
+        f = P3B200ConservationFields()
+        ncol, nlev = fields["qv"].shape
+        for n in CONSERVATION_FIELDS:
+            t = fields.get(n)
+            setattr(f, n, t.data_ptr() if t is not None else None)
+        f.col_stride = fields["qv"].stride(0)
+        w = fields["horiz_winds"]
+        f.wind_col_stride, f.wind_comp_stride = w.stride(0), w.stride(1)
+        return f, ncol, nlev
+
+    def column_conservation_begin(self, fields, stream=None):
+        """compute_current_mass / compute_current_energy of MassAndEnergyColumnConservationCheck on device tensors."""
+        f, ncol, nlev = self._conservation_struct(fields)
+        check(self._L.p3b200_column_conservation_begin(self._h, ctypes.byref(f), ncol, nlev,
+                                                       ctypes.c_void_p(stream) if stream else None), "conservation_begin")
+
+    def column_conservation_check(self, fields, dt, mass_tol, energy_tol, stream=None):
+        f, ncol, nlev = self._conservation_struct(fields)
+        r = P3B200ConservationResult()
+        check(self._L.p3b200_column_conservation_check(self._h, ctypes.byref(f), ncol, nlev, ctypes.c_double(dt),
+                                                       ctypes.c_double(mass_tol), ctypes.c_double(energy_tol),
+                                                       ctypes.byref(r), ctypes.c_void_p(stream) if stream else None),
+              "conservation_check")
+        out = {k: getattr(r, k) for k, _ in r._fields_}
+        arrs = [np.zeros(ncol) for _ in range(4)]
+        check(self._L.p3b200_column_conservation_get(self._h, ncol, *[a.ctypes.data_as(ctypes.c_void_p) for a in arrs]),
+              "conservation_get")
+        out["mass_prev"], out["energy_prev"], out["rel_mass"], out["rel_energy"] = arrs
+        return out
 
     def get_diag(self, ncol):
         out = np.empty((ncol, NUM_DIAG), dtype=np.int32)
