@@ -24,7 +24,7 @@ DEPS = SRC + [os.path.join(ROOT, "scream_b200", "csrc", f) for f in
 # few pow calls by 1-ulp-equivalent cheaper forms -> compared on the well-conditioned columns)
 # "parity" (-DP3B200_PARITY = exact order + the shared deterministic transcendentals of p3_math.hpp): has to match
 # the oracle in shared-math mode BIT FOR BIT on every column; it is the CPU twin of libp3b200_parity.so
-LIB_PATHS = {"exact": os.path.join(ROOT, "build", "libp3hostsim_exact.so"),
+LIB_PATHS = {"exact": os.environ.get("P3B200_HOSTSIM_EXACT_LIB", os.path.join(ROOT, "build", "libp3hostsim_exact.so")),   # override: tools/hostsim_sanitize.sh
              "product": os.path.join(ROOT, "build", "libp3hostsim.so"),
              "parity": os.path.join(ROOT, "build", "libp3hostsim_parity.so")}
 
@@ -35,7 +35,7 @@ _tables = None
 def build(flavour="exact"):
     path = LIB_PATHS[flavour]
     stale = (not os.path.exists(path)) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in DEPS)
-    if stale:
+    if stale and not (flavour == "exact" and "P3B200_HOSTSIM_EXACT_LIB" in os.environ):
         os.makedirs(os.path.dirname(path), exist_ok=True)
         extra = {"exact": ["-DP3B200_EXACT_MATH"], "parity": ["-DP3B200_PARITY"], "product": []}[flavour]
         subprocess.check_call(["g++", "-O2", "-march=x86-64-v3", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared",
