@@ -39,7 +39,7 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 constexpr int NQUEUE = 64;        // ring of work-queue counter groups so p3_main calls in flight on different streams never share one
 constexpr int QSTRIDE = 32;       // counters per group: one per sedimentation launch (3 species x NUM_SED_CLASSES), one per part2 group, pad
-constexpr int NSLOT = 3;          // host pipeline depth (H2D / kernel / D2H in flight)
+constexpr int NSLOT = 4;          // host pipeline depth (H2D / kernel / D2H in flight, one spare)
 
 // events around and between the five launches of one p3_main: m[0] = start, m[EV_END] = end
 struct EventPair { cudaEvent_t m[NUM_PHASE_MARKS] = {nullptr}; };

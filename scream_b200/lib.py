@@ -288,10 +288,11 @@ class P3Handle:
               "p3b200_main")
 
     def main_host(self, fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None, zero_flux_top=True,
-                  want_diag=True):
-        """p3_main on host numpy arrays through the chunked H2D/kernel/D2H pipeline, in place."""
+                  want_diag=True, zero_history=False):
+        """p3_main on host numpy arrays through the chunked H2D/kernel/D2H pipeline, in place.  zero_history: the
+        call zero-fills the three history arrays itself (they are then not copied to the device)."""
         f, ncol, nlev = self.fields_struct(fields, host=True)
-        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, zero_history=zero_history)
         us = ctypes.c_int64(0)
         diag = np.full((ncol, NUM_DIAG), -7, dtype=np.int32) if want_diag else None
         check(self._L.p3b200_main_host(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
