@@ -46,8 +46,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="ne256pg2_L128", choices=sorted(WORKLOADS))
-    ap.add_argument("--ic", default="mixed", choices=["mixed", "random"],
-                    help="mixed: tiled ic::Factory::mixed (G1); random: seeded per-column cloud layers (G2)")
+    ap.add_argument("--ic", default="mixed", choices=["mixed", "mixed_sp", "random"],
+                    help="mixed: tiled ic::Factory::mixed (G1); mixed_sp: the same without its cloudy level at 191 K, where the "
+                         "reference itself overflows in single precision; random: seeded per-column cloud layers (G2)")
     ap.add_argument("--ncol", type=int, default=0, help="override the workload's global column count")
     ap.add_argument("--e2e-cols", type=int, default=98304, help="columns of the e2e (host-buffer) sample per rank")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target CPU work for the cpu_baseline sample")
@@ -86,8 +87,8 @@ def workload_config(args, world, ncol_g, ncol, nlev, dt):
 
 def make_tile(ic, ncols, nlev, dtype):
     """Host tile of distinct columns that the device grid repeats."""
-    if ic == "mixed":
-        return ic_cases.make_mixed_tiled(ncols, nlev, tile=3, dtype=dtype)
+    if ic in ("mixed", "mixed_sp"):
+        return ic_cases.make_mixed_tiled(ncols, nlev, tile=3, dtype=dtype, single_precision_safe=(ic == "mixed_sp"))
     return ic_cases.make_random(ncols, nlev, dtype=dtype)
 
 
@@ -269,7 +270,7 @@ def run_b200(args):
     predict_nc, prescribed_ccn = True, True
 
     # ---- device-resident inputs: a host tile of distinct columns repeated on the device ----------
-    tile_cols = 3 if args.ic == "mixed" else 8192
+    tile_cols = 3 if args.ic in ("mixed", "mixed_sp") else 8192
     tile = make_tile(args.ic, tile_cols, nlev, dtype)
     idx = (torch.arange(ncol, device=dev) + (rank * ncol_g // world if args.scaling == "strong" else 0)) % tile_cols
     fields = {}
@@ -538,7 +539,7 @@ def run_b200(args):
     # IC above tiles 3 distinct columns (the reference's own ic::Factory::mixed), the friendliest input for class-sorted
     # kernels; this one has load imbalance in every tile, window and work queue.  Same arrays, same timing protocol.
     alt = None
-    if not args.no_alt and args.ic == "mixed":
+    if not args.no_alt and args.ic in ("mixed", "mixed_sp"):
         try:
             atile_cols = 8192
             atile = make_tile("random", atile_cols, nlev, dtype)

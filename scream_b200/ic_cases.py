@@ -83,9 +83,23 @@ def make_mixed(ncol, nlev, dtype=np.float64):
     return d
 
 
-def make_mixed_tiled(ncol, nlev, tile=3, dtype=np.float64):
+def drop_cold_cloud(fields, t_min=235.0):
+    """Single-precision variant of `mixed`: cloud water at T < t_min removed.  With 128 levels the reference IC puts a
+    cloudy level at T = 191 K, where Bigg immersion freezing evaluates exp(0.65*(273.15 - T)) = 1.5e23 times gamma
+    factors: the REFERENCE ITSELF overflows binary32 there (its own single-precision build returns inf/NaN in qv and th
+    at that level, oracle/_ref sp build) — the case is outside what P3 can do in single precision."""
+    T = fields["th"].astype(np.float64) / fields["inv_exner"].astype(np.float64)
+    cold = T < t_min
+    for n in ("qc", "nc"):
+        fields[n][cold] = 0
+    return fields
+
+
+def make_mixed_tiled(ncol, nlev, tile=3, dtype=np.float64, single_precision_safe=False):
     """G1: column i := mixed(tile, nlev)[i % tile]."""
     base = make_mixed(tile, nlev, dtype)
+    if single_precision_safe:
+        base = drop_cold_cloud(base)
     idx = np.arange(ncol) % tile
     return {n: np.ascontiguousarray(v[idx]) for n, v in base.items()}
 
