@@ -130,6 +130,7 @@ struct PhaseA {
   static P3_HD Real sp(double x) { return static_cast<Real>(x); }
   // bit pattern of +0.0 (a -0.0 is stored: only the value the memory already holds may be skipped)
   static P3_HD bool is_pos_zero(Real x) { return x == 0 && !std::signbit(x); }
+  static P3_HD bool same_bits(Real a, Real b) { return (a == b && std::signbit(a) == std::signbit(b)) || (a != a && b != b); }
 
   // ---- pass 1 -----------------------------------------------------------------------------------
   struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres; };
@@ -235,9 +236,14 @@ struct PhaseA {
     }
     // the level is complete: every hydrometeor was clipped into vapour (p3_main_impl_part1.hpp:123-175),
     // part2 does not run (p3_main_impl.hpp:211-217: its outputs stay zero)
-    cp.template p<F_QC>(a)[k] = 0; cp.template p<F_NC>(a)[k] = 0; cp.template p<F_QR>(a)[k] = 0; cp.template p<F_NR>(a)[k] = 0;
-    cp.template p<F_QI>(a)[k] = 0; cp.template p<F_QM>(a)[k] = 0; cp.template p<F_NI>(a)[k] = 0; cp.template p<F_BM>(a)[k] = 0;
-    cp.template p<F_QV>(a)[k] = qv; cp.template p<F_TH>(a)[k] = th;
+    // the five values this pass has loaded are stored only where their bits change (a clear level stays clear)
+    if (!is_pos_zero(in.qc)) cp.template p<F_QC>(a)[k] = 0;
+    if (!is_pos_zero(in.qr)) cp.template p<F_QR>(a)[k] = 0;
+    if (!is_pos_zero(in.qi)) cp.template p<F_QI>(a)[k] = 0;
+    cp.template p<F_NC>(a)[k] = 0; cp.template p<F_NR>(a)[k] = 0;
+    cp.template p<F_QM>(a)[k] = 0; cp.template p<F_NI>(a)[k] = 0; cp.template p<F_BM>(a)[k] = 0;
+    if (!same_bits(qv, in.qv)) cp.template p<F_QV>(a)[k] = qv;
+    if (!same_bits(th, in.th)) cp.template p<F_TH>(a)[k] = th;
     cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = 0; cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = 0; cp.template p<F_NEVAPR>(a)[k] = 0;
     cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
     cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = (T < C::T_homogfrz) ? -T0 : T0;
