@@ -346,10 +346,10 @@ def run_b200(args):
         peak = 6650.0; peak_src = "fallback (B200_PROFILING.md 6.65 TB/s)"
     bpl = algorithmic_bytes_per_col_level(rb, predict_nc, prescribed_ccn)
     n_sed = 3 * (1 if nlev <= 32 else 2 if nlev <= 64 else 3 if nlev <= 128 else 4)   # one launch per species and register-window class
-    n_launch = 1 + n_sed + 1
+    n_launch = 8 + n_sed + 1     # phase A: classification pass + six part2 groups + column finish
     achieved = bpl * ncol * nlev / (total_ms / args.steps * 1e-3) / 1e9
-    # measured DRAM traffic of one p3_main (all launches), from the committed ncu capture: bytes per column-level of
-    # the same IC at 148 000 columns (ncu cannot replay the 72 GB working set), scaled to this shard
+    # measured DRAM traffic of one p3_main (all launches), from the committed ncu capture of ONE step at the full
+    # ne256pg2 grid (profiles/r02o_dram_traffic_full_grid.txt): bytes per column-level of the same IC, scaled to this shard
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
@@ -359,7 +359,7 @@ def run_b200(args):
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": f"p3_main = p3_phase_a + {n_sed} x p3_sediment<cloud|rain|ice, window class> + p3_phase_c ({n_launch} launches, one event bracket); dominant: p3_phase_a",
+                "traffic": traffic, "kernel": f"p3_main = p3_classify + 6 x p3_part2<group> + p3_column_finish + {n_sed} x p3_sediment<cloud|rain|ice, window class> + p3_phase_c ({n_launch} launches, one event bracket); longest single kernel: p3_sediment<rain, 1 slot> (phase_ms_last_step)",
                 "bytes_per_column_level": bpl, "peak_source": peak_src}
 
     # ---- e2e: pinned host buffers through p3b200_main_host ---------------------------------------

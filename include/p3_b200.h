@@ -161,7 +161,10 @@ int  p3b200_tables_read_blob(const char* path, const char* expect_version, P3B20
 int  p3b200_tables_generate_rain(P3B200Tables* out);
 
 /* ---- handle ------------------------------------------------------------------------------------ */
-/* real_bytes: 8 (SCREAM_DOUBLE_PRECISION) or 4.  device: CUDA ordinal.  Tables are copied to the device. */
+/* real_bytes: 8 (SCREAM_DOUBLE_PRECISION) or 4.  device: CUDA ordinal.  Tables are copied to the device.
+ * A handle is used by ONE host thread at a time (like the reference: one host thread per rank drives P3,
+ * p3_main_impl.hpp:326); calls on different CUDA streams of one handle are allowed and are ordered where they share
+ * the handle's scratch (the classification pass of a call waits for the previous call's column finish). */
 int p3b200_create(const P3B200Tables* host_tables, int device, int real_bytes, p3b200_handle* out);
 int p3b200_destroy(p3b200_handle h);
 
