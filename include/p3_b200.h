@@ -343,6 +343,17 @@ int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, in
 int p3b200_main_postamble(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
                           const P3B200Infra* infra, const P3B200PostambleFields* post, P3B200CheckResult* checks,
                           void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev);
+/* p3_main with the p3_preamble fused into its first kernel (the streaming classification pass): what run_impl does
+ * before and with P3F::p3_main (eamxx_p3_run.cpp:11-36) in one call.  The pass reads the field manager's wet mixing
+ * ratios, T_mid, p_mid, the two pseudo densities and cldfrac_tot directly, runs the level's p3_preamble
+ * (eamxx_p3_process_interface.hpp:62-129) in registers and stores its results together with its own: the preamble's
+ * separate pass over 31 arrays is gone.  Results are bit-identical to p3b200_preamble followed by p3b200_main (same
+ * operations in the same order per level).  `pre` must name the SAME device arrays as `fields` for every array the
+ * preamble writes (qv qc nc qr nr qi qm ni bm, qv_prev, inv_exner, th_atm, the three cloud fractions, dz), with
+ * pre->col_stride equal to their common column stride (P3B200_EINVAL otherwise). */
+int p3b200_main_preamble(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                         const P3B200Infra* infra, const P3B200PreambleFields* pre, void* cuda_stream,
+                         int64_t* elapsed_us, int32_t* diag_dev);
 /* FieldWithinIntervalCheck::repair_impl (field_within_interval_check.cpp:338-372) for the one repairable check:
  * clip qv into its interval [1e-13, 0.2], in place. */
 int p3b200_repair_qv(p3b200_handle h, void* qv, int64_t col_stride, int32_t ncol, int32_t nlev, void* cuda_stream);

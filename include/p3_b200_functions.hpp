@@ -202,7 +202,8 @@ struct Functions<ScalarT, B200Device> {
                      const P3DiagnosticInputs& diagnostic_inputs, const P3DiagnosticOutputs& diagnostic_outputs,
                      const P3Infrastructure& infrastructure, const P3HistoryOnly& history_only,
                      const P3LookupTables& lookup_tables, const WorkspaceManager& /*workspace_mgr*/,
-                     Int nj, Int nk, void* stream = nullptr, bool zero_history = false) {
+                     Int nj, Int nk, void* stream = nullptr, bool zero_history = false,
+                     const P3B200PreambleFields* fused_preamble = nullptr) {
     if (!lookup_tables.handle) fail(P3B200_EINVAL, "p3_main: lookup tables not initialised (p3_init)");
     P3B200Fields f;
     for (int i = 0; i < P3B200_F_NUM; ++i) { f.ptr[i] = nullptr; f.col_stride[i] = 0; }
@@ -264,7 +265,10 @@ struct Functions<ScalarT, B200Device> {
     // the history arrays are left to run_impl's zero-fill (eamxx_p3_run.cpp:27-29) unless the caller folds it in
     in.zero_history = zero_history ? 1 : 0;
     int64_t us = 0;
-    const int rc = p3b200_main(lookup_tables.handle.get(), &r, &f, &in, stream, &us, nullptr);
+    // fused_preamble (an extension): run_impl's p3_preamble of every level inside p3_main's first kernel
+    const int rc = fused_preamble
+        ? p3b200_main_preamble(lookup_tables.handle.get(), &r, &f, &in, fused_preamble, stream, &us, nullptr)
+        : p3b200_main(lookup_tables.handle.get(), &r, &f, &in, stream, &us, nullptr);
     if (rc) fail(rc, "p3_main");
     int32_t bits = 0;
     if (check_columns && p3b200_error_summary(lookup_tables.handle.get(), &bits) == 0 && bits)

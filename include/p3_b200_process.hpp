@@ -11,8 +11,8 @@
 // checks initialize_impl registers (:226-243) with the repair of qv.
 // What is replaced: the FieldManager/GridsManager (set_grids) by a struct of device pointers named after the fields;
 // Kokkos views by the non-owning PODs of p3_b200_functions.hpp; the ATMBufferManager by a caller-provided device
-// allocation; the three Kokkos launches + 15 reductions of one run_impl by sm_100a kernels (p3b200_preamble,
-// p3b200_main with zero_history, p3b200_postamble_checked).
+// allocation; the three Kokkos launches + 15 reductions of one run_impl by sm_100a kernels (p3b200_main_preamble =
+// p3_preamble inside p3_main's streaming pass, with zero_history; p3b200_postamble_checked).
 //
 // Header-only, C++17, no Kokkos/EKAT.  Errors throw std::logic_error like EKAT_REQUIRE_MSG.
 #ifndef P3_B200_PROCESS_HPP
@@ -201,7 +201,8 @@ class P3MicrophysicsB200 {
     if (!m_initialized) throw std::logic_error("P3Microphysics::run_impl before initialize_impl");
     p3b200_handle h = lookup_tables.handle.get();
     post_.dt = dt;                                                        // p3_postproc.m_dt = dt
-    check(p3b200_preamble(h, &pre_, m_num_cols, m_num_levs, stream), "p3_preamble");      // p3_preproc
+    // p3_preproc: fused into p3_main's first kernel (p3b200_main_preamble) unless fuse_preamble is switched off
+    if (!fuse_preamble) check(p3b200_preamble(h, &pre_, m_num_cols, m_num_levs, stream), "p3_preamble");
     infrastructure.dt = dt;
     infrastructure.it++;
     workspace_mgr.reset_internals();
@@ -231,6 +232,7 @@ class P3MicrophysicsB200 {
   bool qv_was_repaired() const { return m_repaired; }
   Int last_p3_main_microseconds() const { return m_last_p3_main_us; }
   bool fail_on_check = true;
+  bool fuse_preamble = true;
 
   // Keep track of field dimensions and the iteration count
   Int m_num_cols, m_num_levs;
@@ -253,7 +255,8 @@ class P3MicrophysicsB200 {
   }
   Int main_with_zeroed_history(p3b200_handle, void* stream) {
     return P3F::p3_main(runtime_options, prog_state, diag_inputs, diag_outputs, infrastructure, history_only, lookup_tables,
-                        workspace_mgr, m_num_cols, m_num_levs, stream, /*zero_history=*/true);
+                        workspace_mgr, m_num_cols, m_num_levs, stream, /*zero_history=*/true,
+                        fuse_preamble ? &pre_ : nullptr);
   }
 
   Params m_params;

@@ -72,6 +72,7 @@ struct p3b200_ctx {
   size_t scratch_bytes = 0;
   cudaEvent_t scratch_free = nullptr;
   bool scratch_pending = false;
+  const P3B200PreambleFields* pre_for_next = nullptr;   // p3b200_main_preamble: consumed by the next enqueue
   std::vector<EventPair> events;  // one pair per kernel launch of the last call
   size_t events_used = 0;
   int last_ncol = 0;
@@ -178,6 +179,13 @@ int enqueue(p3b200_ctx* h, const P3B200Runtime* runtime, const P3B200Fields* f, 
   P3B200Runtime r;
   if (runtime) r = *runtime; else runtime_defaults(r);
   a.ro = make_runtime<Real>(r);
+  a.pre_pmid = a.pre_pd = a.pre_pdd = a.pre_T = a.pre_cft = nullptr;
+  if (const P3B200PreambleFields* pf = h->pre_for_next) {
+    a.pre_pmid = static_cast<const Real*>(pf->pmid); a.pre_pd = static_cast<const Real*>(pf->pseudo_density);
+    a.pre_pdd = static_cast<const Real*>(pf->pseudo_density_dry); a.pre_T = static_cast<const Real*>(pf->T_atm);
+    a.pre_cft = static_cast<const Real*>(pf->cld_frac_t);
+    if (a.ustride == 0 || a.ustride != pf->col_stride) return P3B200_EINVAL;
+  }
   a.diag = diag;
   a.queue = h->d_queue + h->next_queue * QSTRIDE;
   h->next_queue = (h->next_queue + 1) % NQUEUE;
@@ -362,6 +370,28 @@ static int main_impl(p3b200_handle h, const P3B200Runtime* runtime, const P3B200
 int p3b200_main(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
                 const P3B200Infra* infra, void* cuda_stream, int64_t* elapsed_us, int32_t* diag_dev) {
   return main_impl(h, runtime, fields, infra, cuda_stream, elapsed_us, diag_dev, nullptr, nullptr);
+}
+
+int p3b200_main_preamble(p3b200_handle h, const P3B200Runtime* runtime, const P3B200Fields* fields,
+                         const P3B200Infra* infra, const P3B200PreambleFields* pre, void* cuda_stream,
+                         int64_t* elapsed_us, int32_t* diag_dev) {
+  if (!h || !fields || !infra || !pre) return P3B200_EINVAL;
+  if (pre->col_stride < infra->nlev) return P3B200_EINVAL;
+  // the preamble's outputs are p3_main's inputs: they must be the same arrays, with one column stride
+  struct Alias { const void* p; int f; };
+  const Alias same[] = {{pre->qv, P3B200_F_QV}, {pre->qc, P3B200_F_QC}, {pre->nc, P3B200_F_NC}, {pre->qr, P3B200_F_QR},
+                        {pre->nr, P3B200_F_NR}, {pre->qi, P3B200_F_QI}, {pre->qm, P3B200_F_QM}, {pre->ni, P3B200_F_NI},
+                        {pre->bm, P3B200_F_BM}, {pre->qv_prev, P3B200_F_QV_PREV}, {pre->inv_exner, P3B200_F_INV_EXNER},
+                        {pre->th_atm, P3B200_F_TH}, {pre->cld_frac_l, P3B200_F_CLD_FRAC_L}, {pre->cld_frac_i, P3B200_F_CLD_FRAC_I},
+                        {pre->cld_frac_r, P3B200_F_CLD_FRAC_R}, {pre->dz, P3B200_F_DZ}};
+  for (const Alias& a : same)
+    if (!a.p || a.p != fields->ptr[a.f] || fields->col_stride[a.f] != pre->col_stride) return P3B200_EINVAL;
+  if (!pre->pmid || !pre->pseudo_density || !pre->pseudo_density_dry || !pre->T_atm || !pre->cld_frac_t) return P3B200_EINVAL;
+  // cld_frac_l and cld_frac_i receive the same values but are two arrays of p3_main: they must not alias an input
+  h->pre_for_next = pre;
+  const int rc = main_impl(h, runtime, fields, infra, cuda_stream, elapsed_us, diag_dev, nullptr, nullptr);
+  h->pre_for_next = nullptr;
+  return rc;
 }
 
 int p3b200_get_diag(p3b200_handle h, int32_t* host_out, int32_t ncol) {

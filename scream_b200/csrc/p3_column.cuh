@@ -73,6 +73,10 @@ struct MainArgs {
   Runtime<Real> ro;
   int*    diag;            // [ncol][D_NUM], always present (the handle owns one if the caller passes none)
   unsigned int* queue;     // work-queue counters: one per sedimentation launch (species x window class) and per part2 group, zeroed before phase A
+  // Optional p3_preamble fused into the classification pass (p3b200_main_preamble): the field-manager inputs of
+  // eamxx_p3_process_interface.hpp:62-129.  pre_pmid == nullptr: no preamble.  The arrays the preamble writes are the
+  // p3_main fields themselves (mixing ratios in place, inv_exner, th, the three cloud fractions, dz, qv_prev).
+  const Real *pre_pmid, *pre_pd, *pre_pdd, *pre_T, *pre_cft;
   // phase A scratch owned by the handle (p3_abi.cpp), valid between the classification pass and the column finish:
   unsigned short* wl_idx;  // [ntiles][A_TILE_LEVELS] per tile: tile-local level indices (col_in_tile*nk + k) of the levels part2 has to run on, sorted by class key
   int*            wl_off;  // [ntiles][8]: start of each process group's segment in the tile's list; [6] = number of entries
@@ -133,14 +137,65 @@ struct PhaseA {
   static P3_HD bool same_bits(Real a, Real b) { return (a == b && std::signbit(a) == std::signbit(b)) || (a != a && b != b); }
 
   // ---- pass 1 -----------------------------------------------------------------------------------
-  struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres; };
-  template <bool UNI>
-  static P3_HD void pass1_load(const MainArgs<Real>& a, int64_t col, int k, In1& in) {
+  // m_*: what memory holds for the five values this pass may have to store (with the fused preamble these are the wet
+  // mixing ratios and an undefined th: every value the preamble changes is stored)
+  struct In1 { Real qc, qr, qi, qv, th, inv_exner, pres, m_qc, m_qr, m_qi, m_qv; bool th_in_memory; };
+  struct Pre1 { Real pmid, pd, pdd, T, cft, cft_above, qv_prev; };     // PRE: the preamble's own loads of one level
+  template <bool UNI, bool PRE = false>
+  static P3_HD void pass1_load(const MainArgs<Real>& a, int64_t col, int k, In1& in, Pre1* pre = nullptr) {
     const ColAddr<UNI, Real> cp(a, col);
     in.qc = cp.template p<F_QC>(a)[k]; in.qr = cp.template p<F_QR>(a)[k]; in.qi = cp.template p<F_QI>(a)[k];
-    in.qv = cp.template p<F_QV>(a)[k]; in.th = cp.template p<F_TH>(a)[k];
-    in.inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
+    in.qv = cp.template p<F_QV>(a)[k];
     in.pres = P3_LDG(cp.template p<F_PRES>(a) + k);
+    in.m_qc = in.qc; in.m_qr = in.qr; in.m_qi = in.qi; in.m_qv = in.qv;
+    if (PRE) {
+      const int64_t o = col * a.ustride + k;        // the fused preamble requires the common column stride
+      pre->pmid = P3_LDG(a.pre_pmid + o); pre->pd = P3_LDG(a.pre_pd + o); pre->pdd = P3_LDG(a.pre_pdd + o);
+      pre->T = P3_LDG(a.pre_T + o); pre->cft = P3_LDG(a.pre_cft + o);
+      pre->cft_above = (k != 0) ? P3_LDG(a.pre_cft + o - 1) : Real(0);
+      pre->qv_prev = cp.template p<F_QV_PREV>(a)[k];
+      in.th = 0; in.inv_exner = 1; in.th_in_memory = false;
+    } else {
+      in.th = cp.template p<F_TH>(a)[k];
+      in.inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
+      in.th_in_memory = true;
+    }
+  }
+
+  // p3_preamble of one level (eamxx_p3_process_interface.hpp:62-129; helper formulas
+  // share/util/scream_common_physics_functions_impl.hpp:88-97, 115-118, 214-222, 375-379, 400-409), statement for
+  // statement what p3_preamble_kernel (p3_prepost.cu) does: dz from the wet qv, wet -> dry of the four mixing ratios
+  // this pass reads and of qv_prev, exner / theta, the cloud fractions with the max-overlap rain fraction.  Stores the
+  // six arrays only the preamble defines; the dry qc/qr/qi/qv and th travel on in `in`.
+  template <bool UNI>
+  static P3_HD void preamble_level(const MainArgs<Real>& a, int64_t col, int k, const Pre1& pr, In1& in) {
+    const ColAddr<UNI, Real> cp(a, col);
+    const Real c1 = -Real(1) + Real(1) / C::ep_2;
+    const Real T_virtual = pr.T * (Real(1) + c1 * in.qv);
+    cp.template p<F_DZ>(a)[k] = (C::RD / C::gravit) * pr.pd * T_virtual / pr.pmid;
+    in.qv = in.qv * pr.pd / pr.pdd; in.qc = in.qc * pr.pd / pr.pdd;
+    in.qr = in.qr * pr.pd / pr.pdd; in.qi = in.qi * pr.pd / pr.pdd;
+    cp.template p<F_QV_PREV>(a)[k] = pr.qv_prev * pr.pd / pr.pdd;
+    const Real ex = P::x_pow(pr.pmid / C::P0, C::RD * C::INV_CP);
+    in.inv_exner = Real(1.0) / ex;
+    in.th = pr.T / ex;
+    cp.template p<F_INV_EXNER>(a)[k] = in.inv_exner;
+    const Real mincld = Real(0.0001);
+    const Real cf = pr.cft < mincld ? mincld : pr.cft;
+    cp.template p<F_CLD_FRAC_L>(a)[k] = cf; cp.template p<F_CLD_FRAC_I>(a)[k] = cf;
+    cp.template p<F_CLD_FRAC_R>(a)[k] = (k != 0 && pr.cft_above > cf) ? pr.cft_above : cf;
+  }
+  // ... and of the five mixing ratios the classification pass does not read, on a level part2 will run on
+  template <bool UNI>
+  static P3_HD void preamble_rest_of_level(const MainArgs<Real>& a, int64_t col, int k, const Pre1& pr) {
+    const ColAddr<UNI, Real> cp(a, col);
+    Real* const p[5] = {cp.template p<F_NC>(a) + k, cp.template p<F_NR>(a) + k, cp.template p<F_QM>(a) + k,
+                        cp.template p<F_NI>(a) + k, cp.template p<F_BM>(a) + k};
+    Real v[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) v[i] = *p[i];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) *p[i] = v[i] * pr.pd / pr.pdd;
   }
 
   // Single-precision estimate of qv / qv_sat_i(T0, pres) on a cold level (relative error < 1e-4: fp32
@@ -171,8 +226,8 @@ struct PhaseA {
 
   // Returns -1 when the level is finished (skip_all; state stored), else its sort key in [0, A_NKEYS).
   // `flags` receives CF_NUC / CF_HYD1 / error bits of this level (to be OR-ed into the column's accumulator).
-  template <bool UNI>
-  static P3_HD int pass1_level(const MainArgs<Real>& a, int64_t col, int k, const In1& in, int& flags) {
+  template <bool UNI, bool PRE = false>
+  static P3_HD int pass1_level(const MainArgs<Real>& a, int64_t col, int k, const In1& in, int& flags, const Pre1* pre = nullptr) {
     const ColAddr<UNI, Real> cp(a, col);
     const Real qsmall = C::QSMALL, Tz = C::Tmelt, latvap = C::LatVap, latice = C::LatIce, inv_cp = C::INV_CP;
     if (a.zero_history) {   // the caller's zero-fill of eamxx_p3_run.cpp:27-29, folded into this pass
@@ -230,6 +285,11 @@ struct PhaseA {
       cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = 0; cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = 0; cp.template p<F_NEVAPR>(a)[k] = 0;
       cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
       cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = (T < C::T_homogfrz) ? -T0 : T0;
+      if (PRE) {   // part2 reads its inputs from memory: the preamble's results of this level have to be there
+        cp.template p<F_QC>(a)[k] = in.qc; cp.template p<F_QR>(a)[k] = in.qr; cp.template p<F_QI>(a)[k] = in.qi;
+        cp.template p<F_QV>(a)[k] = in.qv; cp.template p<F_TH>(a)[k] = in.th;
+        preamble_rest_of_level<UNI>(a, col, k, *pre);
+      }
       // temperature regime of Phys::part2_level<GRP>: 0 T > Tmelt, 1 T_rainfrz < T <= Tmelt, 2 T <= T_rainfrz
       const int tc = (T <= C::T_rainfrz) ? 2 : (T <= Tz) ? 1 : 0;
       return (tc << 3) | (int(has_i) << 2) | (int(has_r) << 1) | int(has_c);
@@ -237,13 +297,13 @@ struct PhaseA {
     // the level is complete: every hydrometeor was clipped into vapour (p3_main_impl_part1.hpp:123-175),
     // part2 does not run (p3_main_impl.hpp:211-217: its outputs stay zero)
     // the five values this pass has loaded are stored only where their bits change (a clear level stays clear)
-    if (!is_pos_zero(in.qc)) cp.template p<F_QC>(a)[k] = 0;
-    if (!is_pos_zero(in.qr)) cp.template p<F_QR>(a)[k] = 0;
-    if (!is_pos_zero(in.qi)) cp.template p<F_QI>(a)[k] = 0;
+    if (!is_pos_zero(in.m_qc)) cp.template p<F_QC>(a)[k] = 0;
+    if (!is_pos_zero(in.m_qr)) cp.template p<F_QR>(a)[k] = 0;
+    if (!is_pos_zero(in.m_qi)) cp.template p<F_QI>(a)[k] = 0;
     cp.template p<F_NC>(a)[k] = 0; cp.template p<F_NR>(a)[k] = 0;
     cp.template p<F_QM>(a)[k] = 0; cp.template p<F_NI>(a)[k] = 0; cp.template p<F_BM>(a)[k] = 0;
-    if (!same_bits(qv, in.qv)) cp.template p<F_QV>(a)[k] = qv;
-    if (!same_bits(th, in.th)) cp.template p<F_TH>(a)[k] = th;
+    if (!same_bits(qv, in.m_qv)) cp.template p<F_QV>(a)[k] = qv;
+    if (!in.th_in_memory || !same_bits(th, in.th)) cp.template p<F_TH>(a)[k] = th;
     cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = 0; cp.template p<F_PRECIP_TOTAL_TEND>(a)[k] = 0; cp.template p<F_NEVAPR>(a)[k] = 0;
     cp.template p<F_PRECIP_LIQ_FLUX>(a)[k] = 0; cp.template p<F_PRECIP_ICE_FLUX>(a)[k] = 0;
     cp.template p<F_DIAG_EFF_RADIUS_QC>(a)[k] = (T < C::T_homogfrz) ? -T0 : T0;

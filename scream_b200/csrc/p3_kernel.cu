@@ -84,7 +84,7 @@ constexpr int C_THREADS = P3B200_C_THREADS;
 // column flags and the level's skip_all gate.  skip_all levels are complete and stored here; the others are appended
 // to the tile's list in shared memory (ballot-compacted) with their class key, counting-sorted by key and written to
 // the tile's work list in global memory, where the part2 launches find them (one segment per process group).
-template <typename Real, bool UNI>
+template <typename Real, bool UNI, bool PRE>
 __global__ void __launch_bounds__(A_THREADS, A_MIN_BLOCKS)
 p3_classify(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const unsigned div_magic) {
   __shared__ unsigned short s_idx[A_TILE_LEVELS];      // pass order: level index inside the tile
@@ -106,23 +106,28 @@ p3_classify(const __grid_constant__ MainArgs<Real> a, const int tile_cols, const
   if (tid == 0) s_count = 0;
   __syncthreads();
 
-  // A_P1_UNROLL levels per thread and iteration: all their loads are in flight before any is consumed
-  for (int base = tid - lane; base < nlevels; base += A_P1_UNROLL * A_THREADS) {
-    int idx[A_P1_UNROLL], c[A_P1_UNROLL], k[A_P1_UNROLL], key[A_P1_UNROLL];
-    typename PhaseA<Real>::In1 in[A_P1_UNROLL];
+  // U levels per thread and iteration: all their loads are in flight before any is consumed (one with the fused
+  // preamble: its ~900 instructions per level make the pass issue-bound, and half the code misses the instruction cache less)
+  constexpr int U = PRE ? 1 : A_P1_UNROLL;
+  for (int base = tid - lane; base < nlevels; base += U * A_THREADS) {
+    int idx[U], c[U], k[U], key[U];
+    typename PhaseA<Real>::In1 in[U];
+    typename PhaseA<Real>::Pre1 pre[PRE ? U : 1];
 #pragma unroll
-    for (int u = 0; u < A_P1_UNROLL; ++u) {
+    for (int u = 0; u < U; ++u) {
       key[u] = -1;
       idx[u] = base + u * A_THREADS + lane;
       c[u] = (int)(((unsigned)idx[u] * div_magic) >> 24);      // idx / nk for idx < 8192 (plan_launch checks the magic)
       k[u] = idx[u] - c[u] * nk;
-      if (idx[u] < nlevels) PhaseA<Real>::template pass1_load<UNI>(a, col0 + c[u], k[u], in[u]);
+      if (idx[u] < nlevels) PhaseA<Real>::template pass1_load<UNI, PRE>(a, col0 + c[u], k[u], in[u], &pre[PRE ? u : 0]);
     }
 #pragma unroll
-    for (int u = 0; u < A_P1_UNROLL; ++u) {
+    for (int u = 0; u < U; ++u) {
       if (idx[u] < nlevels) {
         int fl = 0;
-        key[u] = PhaseA<Real>::template pass1_level<UNI>(a, col0 + c[u], k[u], in[u], fl);
+        // p3_preamble of the level first, when it is fused into this pass (P3Microphysics::run_impl, eamxx_p3_run.cpp:11-16)
+        if (PRE) PhaseA<Real>::template preamble_level<UNI>(a, col0 + c[u], k[u], pre[PRE ? u : 0], in[u]);
+        key[u] = PhaseA<Real>::template pass1_level<UNI, PRE>(a, col0 + c[u], k[u], in[u], fl, &pre[PRE ? u : 0]);
         if (fl) atomicOr(&s_flags[c[u]], fl);
         lvl[idx[u]] = 0;
       }
@@ -426,8 +431,12 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream_,
   mark(0, stream);
   {
     const bool uni = a.ustride != 0 && a.ustride_flux != 0;
-    if (uni) p3_classify<Real, true><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
-    else     p3_classify<Real, false><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    if (a.pre_pmid) {
+      if (!uni) return (int)cudaErrorInvalidValue;       // the fused preamble needs the common column stride
+      p3_classify<Real, true, true><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    }
+    else if (uni) p3_classify<Real, true, false><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
+    else          p3_classify<Real, false, false><<<cfg.a_blocks, A_THREADS, 0, stream>>>(a, cfg.a_tile_cols, cfg.a_div_magic);
     mark(7, stream);
 #define P3_LAUNCH_P2(G, S) \
     if (uni) p3_part2<Real, G, true><<<cfg.p2_blocks, P2_THREADS, 0, S>>>(a, cfg.a_blocks, cfg.a_tile_cols, cfg.a_div_magic); \

@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "p3b200_tables_generate_rain", "p3b200_create", "p3b200_destroy", "p3b200_main", "p3b200_get_diag",
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
     "p3b200_last_sed_concurrent", "p3b200_last_phase_a_ms",
-    "p3b200_column_conservation_begin", "p3b200_column_conservation_check", "p3b200_column_conservation_get",
+    "p3b200_main_preamble", "p3b200_column_conservation_begin", "p3b200_column_conservation_check", "p3b200_column_conservation_get",
     "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
@@ -102,6 +102,8 @@ def lib(flavour="product"):
         L.p3b200_last_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
         L.p3b200_last_sed_concurrent.argtypes = [ctypes.c_void_p]
         L.p3b200_last_phase_a_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]
+        L.p3b200_main_preamble.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_column_conservation_begin.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
         L.p3b200_column_conservation_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
                                                        ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p,
@@ -265,6 +267,21 @@ class P3Handle:
         check(self._L.p3b200_main(self._h, ctypes.byref(runtime) if runtime is not None else None, ctypes.byref(f),
                                 ctypes.byref(infra), sptr, ctypes.byref(us) if timed else None, dptr), "p3b200_main")
         return us.value if timed else None
+
+    def main_preamble(self, fields, pre_fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None,
+                      zero_flux_top=True, stream=None, zero_history=False):
+        """p3_preamble fused into p3_main's classification pass (p3b200_main_preamble); `pre_fields` aliases `fields`
+        for every array the preamble writes."""
+        f, ncol, nlev = self.fields_struct(fields, host=False)
+        infra = self._infra(ncol, nlev, dt, predict_nc, prescribed_ccn, zero_flux_top, zero_history=zero_history)
+        pf = P3B200PreambleFields()
+        for n in PREAMBLE_FIELDS:
+            setattr(pf, n, pre_fields[n].data_ptr())
+        pf.col_stride = pre_fields["qv"].stride(0)
+        sptr = ctypes.c_void_p(stream) if stream else None
+        check(self._L.p3b200_main_preamble(self._h, ctypes.byref(runtime) if runtime is not None else None,
+                                           ctypes.byref(f), ctypes.byref(infra), ctypes.byref(pf), sptr, None, None),
+              "p3b200_main_preamble")
 
     def main_postamble(self, fields, post_fields, dt, predict_nc=True, prescribed_ccn=True, runtime=None,
                        zero_flux_top=True, stream=None, checks=False):

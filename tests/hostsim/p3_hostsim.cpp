@@ -44,7 +44,7 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   for (int f = 0; f < F_NUM; ++f) { a.f[f] = static_cast<Real*>(fields[f]); a.stride[f] = strides[f]; }
   a.ncol = ncol; a.nk = nlev; a.dt = Real(dt); a.predictNc = predictNc; a.prescribedCCN = prescribedCCN;
   a.zero_flux_top = zero_flux_top; a.ustride = 0; a.ustride_flux = 0;
-  a.zero_history = 0; a.wl_idx = nullptr; a.wl_off = nullptr; a.lvlflags = nullptr;
+  a.zero_history = 0; a.pre_pmid = a.pre_pd = a.pre_pdd = a.pre_T = a.pre_cft = nullptr; a.wl_idx = nullptr; a.wl_off = nullptr; a.lvlflags = nullptr;
   a.tb = Tables<Real>{ice.data(), coll.data(), vn.data(), vm.data(), revap.data(), vmn.data()};
   typename Phys<Real>::Loc3 tj;
   Phys<Real>::lookup3_from_dum1(Real(rt ? rt->constant_mu_rain : 1.0), Real(0), tj);

@@ -191,3 +191,54 @@ def test_fused_main_postamble_rejects_foreign_arrays(p3lib):
     with pytest.raises(Exception):
         h.main_postamble(m, p, 300.0, True, True)
     h.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("ic", ["mixed", "random"])
+def test_preamble_fused_into_p3_main_is_bit_identical_to_the_two_calls(p3lib, dtype, ic):
+    """p3b200_main_preamble (the p3_preamble of every level run inside the streaming classification pass) against
+    p3b200_preamble followed by p3b200_main on the same field-manager state: every array either call writes."""
+    torch = pytest.importorskip("torch")
+    from scream_b200.fields import FIELDS
+    from tests import test_gpu_process as tp
+    ncol, nlev, dt = 700, 128, 300.0
+    fm = tp.field_manager_state(ncol, nlev, seed=3, ic=ic)
+    rb = np.dtype(dtype).itemsize
+    h = p3lib.P3Handle(0, rb)
+
+    def run(fused):
+        d = {k: torch.from_numpy(v.astype(dtype)).cuda() for k, v in fm.items()}
+        new = lambda *s: torch.full(s, -7.0, dtype=d["qv"].dtype, device="cuda")  # noqa: E731
+        buf = {n: new(ncol, nlev) for n in ("inv_exner", "th_atm", "cld_frac_l", "cld_frac_i", "dz")}
+        pre = {"pmid": d["p_mid"], "pseudo_density": d["pseudo_density"], "pseudo_density_dry": d["pseudo_density_dry"],
+               "T_atm": d["T_mid"], "cld_frac_t": d["cldfrac_tot"], "qv_prev": d["qv_prev_micro_step"],
+               "cld_frac_r": d["rainfrac"], **buf}
+        for n in ("qv", "qc", "nc", "qr", "nr", "qi", "qm", "ni", "bm"):
+            pre[n] = d[n]
+        main = {"qc": d["qc"], "nc": d["nc"], "qr": d["qr"], "nr": d["nr"], "qi": d["qi"], "qm": d["qm"], "ni": d["ni"],
+                "bm": d["bm"], "qv": d["qv"], "th": buf["th_atm"], "nc_nuceat_tend": d["nc_nuceat_tend"], "nccn": d["nccn"],
+                "ni_activated": d["ni_activated"], "inv_qc_relvar": d["inv_qc_relvar"], "cld_frac_i": buf["cld_frac_i"],
+                "cld_frac_l": buf["cld_frac_l"], "cld_frac_r": d["rainfrac"], "pres": d["p_dry_mid"], "dz": buf["dz"],
+                "dpres": d["pseudo_density_dry"], "inv_exner": buf["inv_exner"], "qv_prev": d["qv_prev_micro_step"],
+                "t_prev": d["T_prev_micro_step"], "qv2qi_depos_tend": new(ncol, nlev), "diag_eff_radius_qc": d["eff_radius_qc"],
+                "diag_eff_radius_qi": d["eff_radius_qi"], "diag_eff_radius_qr": d["eff_radius_qr"], "rho_qi": new(ncol, nlev),
+                "precip_liq_flux": new(ncol, nlev + 1), "precip_ice_flux": new(ncol, nlev + 1),
+                "precip_total_tend": d["precip_total_tend"], "nevapr": d["nevapr"],
+                "liq_ice_exchange": d["micro_liq_ice_exchange"], "vap_liq_exchange": d["micro_vap_liq_exchange"],
+                "vap_ice_exchange": d["micro_vap_ice_exchange"], "precip_liq_surf": new(ncol), "precip_ice_surf": new(ncol)}
+        assert set(main) == set(FIELDS)
+        if fused:
+            h.main_preamble(main, pre, dt, True, True, zero_history=True)
+        else:
+            h.preamble(pre)
+            h.main(main, dt, True, True, zero_history=True)
+        torch.cuda.synchronize()
+        out = {k: v.cpu().numpy() for k, v in main.items()}
+        out.update({"pre_" + k: v.cpu().numpy() for k, v in pre.items()})
+        return out, h.get_diag(ncol)
+
+    (a, da), (b, db) = run(False), run(True)
+    assert np.array_equal(da, db)
+    for n in a:
+        assert np.array_equal(a[n], b[n], equal_nan=True), n
+    h.close()
