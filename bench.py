@@ -473,7 +473,7 @@ def run_b200(args):
                 handle.main_postamble(fields, post, dt, predict_nc, prescribed_ccn)
 
             tail = {}
-            for name, fn in (("main_then_postamble", two_calls), ("main_postamble_fused", fused)):
+            for name, fn in (("main_then_postamble", two_calls), ("main_postamble_one_call", fused)):
                 ms = []
                 for it in range(4):
                     restore()

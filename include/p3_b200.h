@@ -331,12 +331,11 @@ int p3b200_property_checks(p3b200_handle h, const P3B200CheckFields* f, int32_t 
                            P3B200CheckResult out[P3B200_NUM_CHECKS], void* cuda_stream);
 int p3b200_postamble_checked(p3b200_handle h, const P3B200PostambleFields* f, int32_t ncol, int32_t nlev,
                              P3B200CheckResult out[P3B200_NUM_CHECKS], void* cuda_stream);
-/* p3_main with the postamble fused into its last kernel: what P3Microphysics::run_impl does after the preamble
- * (eamxx_p3_run.cpp:26-44), in one call.  Phase C is one thread per (column, level); the thread that has just
- * written th, the mixing ratios and the effective radii of its level runs the p3_postamble of that level as its
- * tail (T from theta with the dry/wet rescaling, dry -> wet, radii to microns, T_prev / qv_prev, the per-column
- * masses at level 0) — the second pass over 32 arrays of the stand-alone postamble is gone.  Results are bit-identical
- * to p3b200_main followed by p3b200_postamble (same operations in the same order per level).
+/* p3_main followed by p3_postamble in one call: what P3Microphysics::run_impl does after the preamble
+ * (eamxx_p3_run.cpp:26-44).  The postamble (T from theta with the dry/wet rescaling, dry -> wet, radii to microns,
+ * T_prev / qv_prev, the per-column masses at level 0) is enqueued behind phase C as its own streaming launch.  (Round 1
+ * ran it as the tail of phase C; that was measured slower than the two launches and has been removed.)  Results are
+ * those of p3b200_main followed by p3b200_postamble.
  * `post` must name the SAME device arrays as `fields` for th_atm/qv/qc/nc/qr/nr/qi/qm/ni/bm, the three radii and
  * the two surface fluxes (P3B200_EINVAL otherwise), with post->col_stride equal to their column stride.
  * checks: NULL, or P3B200_NUM_CHECKS results filled as by p3b200_postamble_checked (the call then synchronises). */

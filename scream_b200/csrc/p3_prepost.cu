@@ -385,6 +385,8 @@ int clip_field(void* field, int64_t stride, int ncol, int nk, double lb, double 
   return (int)cudaGetLastError();
 }
 
+template int launch_postamble<double>(const PostArgs<double>&, void*);
+template int launch_postamble<float>(const PostArgs<float>&, void*);
 template int preamble_from_abi<double>(const P3B200PreambleFields*, int, int, void*);
 template int preamble_from_abi<float>(const P3B200PreambleFields*, int, int, void*);
 template PostArgs<double> make_post_args<double>(const P3B200PostambleFields*, int, int, unsigned*);

@@ -31,6 +31,10 @@ struct PostArgs {
 template <typename Real>
 PostArgs<Real> make_post_args(const P3B200PostambleFields* f, int ncol, int nlev, unsigned* check_mask);
 
+// p3_postamble over all levels of `a` on `stream` (p3_prepost.cu); folds the property-check mask in when a.check_mask
+template <typename Real>
+int launch_postamble(const PostArgs<Real>& a, void* stream);
+
 #if defined(__CUDACC__)
 template <typename Real>
 struct PrePost {
