@@ -38,6 +38,7 @@ extern "C" {
 #define P3B200_ETABLE   -4   /* lookup-table blob/text malformed or wrong version (p3_table_ice_impl.hpp:40-41) */
 #define P3B200_ECOLUMN  -5   /* a column raised a physics error flag (T<=0 / NaN / Co_max<0), see diag[P3B200_D_ERROR] */
 #define P3B200_EINTERNAL -6  /* two evaluations of the same property check disagree (fields modified concurrently?) */
+#define P3B200_ETOOBIG  -7   /* more columns than an allocation-free entry point's fixed scratch holds */
 
 #define P3B200_MAX_NLEV 256  /* levels per column supported by the warp-per-column layout (8 per lane) */
 
@@ -216,6 +217,26 @@ int p3b200_last_sed_concurrent(p3b200_handle h);
  * (result in totals4_dev); with totals4_host != NULL it also copies the result back and synchronises. */
 int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
                                void* cuda_stream, double* totals4_dev, double* totals4_host);
+
+/* ---- the same totals without any allocation ---------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * p3b200_water_energy_totals keeps its scratch (4 doubles per column + the partial sums) in a block the handle
+ * allocates and grows on demand; this variant runs the same three kernels with that scratch in a file-scope
+ * `static __device__` array of the library (p3_budget.cu), so the call itself performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine, copies nothing back and does not synchronise: the result (the same 4 doubles,
+ * bit for bit) lands in totals4_dev, a DEVICE buffer of the caller's, in stream order on cuda_stream.
+ *   limit   infra->ncol <= P3B200_STATIC_BUDGET_MAX_COLS; beyond it the call launches nothing and returns
+ *           P3B200_ETOOBIG with the sizes in p3b200_last_cuda_error().  Shard larger domains, or use the variant above.
+ *   cost    every GPU that loads the library holds the array, 1 MiB + 8 KiB, until the process exits.
+ *   sharing all calls on a device (any handle, any stream) share the array, which keeps the last call's contents;
+ *           nothing in it has to start at zero (every word read has been written earlier in the same call), but two
+ *           calls that can overlap on the GPU race: order them on one stream or with events.
+ *   set-up  the first call on each device looks the array's device address up (cudaGetSymbolAddress, not an
+ *           allocation, but not something to do inside a graph capture): make one call per device beforehand. */
+#define P3B200_STATIC_BUDGET_MAX_COLS 32768
+int p3b200_water_energy_totals_static(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
+                                      void* cuda_stream, double* totals4_dev);
 
 /* ---- the column conservation check the atmosphere driver wraps around a process --------------------------
  * MassAndEnergyColumnConservationCheck (share/property_checks/mass_and_energy_column_conservation_check.cpp): before

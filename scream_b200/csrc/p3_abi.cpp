@@ -246,6 +246,7 @@ const char* p3b200_strerror(int code) {
     case P3B200_ETABLE: return "lookup table malformed or wrong version";
     case P3B200_ECOLUMN: return "a column raised a physics error flag";
     case P3B200_EINTERNAL: return "two evaluations of a property check disagree";
+    case P3B200_ETOOBIG: return "size beyond the fixed maximum of an allocation-free entry point (see p3b200_last_cuda_error)";
     default: return "unknown error";
   }
 }
@@ -475,6 +476,37 @@ int p3b200_water_energy_totals(p3b200_handle h, const P3B200Fields* fields, cons
   return P3B200_OK;
 }
 
+// No allocation on this path: the scratch is the file-scope device array of p3_budget.cu (launch_budget_static), the
+// result goes to the caller's device buffer, and nothing is copied back or synchronised.
+int p3b200_water_energy_totals_static(p3b200_handle h, const P3B200Fields* fields, const P3B200Infra* infra,
+                                      void* cuda_stream, double* totals4_dev) {
+  if (!h || !fields || !infra || !totals4_dev || infra->ncol < 0 || infra->nlev < 1) return P3B200_EINVAL;
+  if (infra->ncol > P3B200_STATIC_BUDGET_MAX_COLS) {
+    g_last_cuda_error = "p3b200_water_energy_totals_static: ncol = " + std::to_string(infra->ncol) +
+                        " exceeds P3B200_STATIC_BUDGET_MAX_COLS = " + std::to_string(P3B200_STATIC_BUDGET_MAX_COLS) +
+                        " (use p3b200_water_energy_totals, or split the columns)";
+    return P3B200_ETOOBIG;
+  }
+  static const int need[] = {P3B200_F_QV, P3B200_F_QC, P3B200_F_QI, P3B200_F_QR, P3B200_F_TH, P3B200_F_INV_EXNER,
+                             P3B200_F_DPRES, P3B200_F_PRECIP_LIQ_SURF, P3B200_F_PRECIP_ICE_SURF};
+  for (int i : need) if (!fields->ptr[i]) return P3B200_EINVAL;
+  CU(cudaSetDevice(h->device));
+  int rc;
+  if (h->real_bytes == 8) {
+    MainArgs<double> a{};
+    for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<double*>(fields->ptr[i]); a.stride[i] = fields->col_stride[i]; }
+    a.ncol = infra->ncol; a.nk = infra->nlev; a.dt = infra->dt;
+    rc = launch_budget_static<double>(a, totals4_dev, cuda_stream);
+  } else {
+    MainArgs<float> a{};
+    for (int i = 0; i < F_NUM; ++i) { a.f[i] = static_cast<float*>(fields->ptr[i]); a.stride[i] = fields->col_stride[i]; }
+    a.ncol = infra->ncol; a.nk = infra->nlev; a.dt = float(infra->dt);
+    rc = launch_budget_static<float>(a, totals4_dev, cuda_stream);
+  }
+  if (rc) return cuda_fail((cudaError_t)rc, "static budget launches");
+  return P3B200_OK;
+}
+
 int p3b200_preamble(p3b200_handle h, const P3B200PreambleFields* f, int32_t ncol, int32_t nlev, void* cuda_stream) {
   if (!h || !f || ncol < 0 || nlev < 1 || f->col_stride < nlev) return P3B200_EINVAL;
   const void* need[] = {f->pmid, f->pseudo_density, f->pseudo_density_dry, f->T_atm, f->cld_frac_t, f->qv, f->qc, f->nc,
@@ -512,6 +544,7 @@ int p3b200_postamble(p3b200_handle h, const P3B200PostambleFields* f, int32_t nc
 // ---- property checks (eamxx_p3_process_interface.cpp:226-243) ----
 namespace {
 static_assert((int)CHK_NUM == (int)P3B200_NUM_CHECKS, "check tables out of step");
+static_assert(STATIC_BUDGET_MAX_COLS == P3B200_STATIC_BUDGET_MAX_COLS, "static budget scratch out of step with the header");
 struct CheckSpec { double lb, ub; bool can_repair; bool column_field; };
 inline CheckSpec check_spec(int i) { return {CHK_LB[i], CHK_UB[i], CHK_CAN_REPAIR[i], CHK_COLUMN_FIELD[i]}; }
 

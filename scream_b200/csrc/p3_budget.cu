@@ -14,6 +14,8 @@
 
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 namespace p3b200 {
 
 constexpr int BUD_WARPS = 8;
@@ -197,5 +199,49 @@ template int launch_conservation<float>(const ConsArgs<float>&, bool, double*, d
 
 template int launch_budget<double>(const MainArgs<double>&, double*, double*, int, double*, void*);
 template int launch_budget<float>(const MainArgs<float>&, double*, double*, int, double*, void*);
+
+// =================================================================================================
+// The allocation-free variant of the budget (p3b200_water_energy_totals_static; no counterpart in the reference).
+// The scratch of the three kernels above — col_vals[ncol][4] and the BUDGET_PARTS*4 partial sums — lives in a
+// file-scope device array of a fixed size instead of the handle's cudaMalloc'ed block.  Every GPU that loads this
+// library holds the array (STATIC_BUDGET_MAX_COLS*32 + BUDGET_PARTS*32 bytes = 1 MiB + 8 KiB) until the process ends.
+//
+// In HOST code the name g_budget_static is only a stand-in for the symbol, not a device address: the address a kernel
+// can use comes from cudaGetSymbolAddress, asked once per device with that device current, and is kept per device.
+// Nothing in the array has to start at zero: p3_column_budget writes all 4 values of every column < ncol before
+// p3_budget_partials reads them, and every one of the BUDGET_PARTS blocks writes its partial (an empty range writes
+// zeros) before p3_budget_final reads them.  The array keeps the last call's contents, and all calls on a device share
+// it: two calls that overlap on the GPU (different streams, no ordering between them) race.
+static __device__ __align__(256) double g_budget_static[(size_t)STATIC_BUDGET_MAX_COLS * 4 + BUDGET_PARTS * 4];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mutex;
+double* g_static_addr[STATIC_MAX_DEVICES] = {};   // device address of g_budget_static, per device ordinal
+}  // namespace
+
+// Returns a cudaError_t as int.  The current device is the one the caller (the ABI entry point) has selected.
+template <typename Real>
+int launch_budget_static(const MainArgs<Real>& a, double* totals4, void* stream) {
+  if (a.ncol > STATIC_BUDGET_MAX_COLS) return (int)cudaErrorInvalidValue;   // the entry point has rejected it already
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return (int)cudaErrorInvalidDevice;
+  double* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_addr[dev]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_budget_static);
+      if (e != cudaSuccess) return (int)e;
+      g_static_addr[dev] = static_cast<double*>(p);
+    }
+    base = g_static_addr[dev];
+  }
+  return launch_budget<Real>(a, base, base + (size_t)STATIC_BUDGET_MAX_COLS * 4, BUDGET_PARTS, totals4, stream);
+}
+template int launch_budget_static<double>(const MainArgs<double>&, double*, void*);
+template int launch_budget_static<float>(const MainArgs<float>&, double*, void*);
 
 }  // namespace p3b200

@@ -71,6 +71,11 @@ int launch_main(const MainArgs<Real>& a, const LaunchConfig& cfg, void* stream, 
 constexpr int BUDGET_PARTS = 256;
 template <typename Real>
 int launch_budget(const MainArgs<Real>& a, double* col_vals, double* partials, int nparts, double* totals4, void* stream);
+// The same three kernels with their scratch in a file-scope __device__ array of p3_budget.cu (no allocation anywhere);
+// at most STATIC_BUDGET_MAX_COLS columns (= P3B200_STATIC_BUDGET_MAX_COLS of the public header).
+constexpr int STATIC_BUDGET_MAX_COLS = 32768;
+template <typename Real>
+int launch_budget_static(const MainArgs<Real>& a, double* totals4, void* stream);
 
 // MassAndEnergyColumnConservationCheck (p3_budget.cu).  check = false: compute_current_mass / compute_current_energy
 // into mass[ncol] / energy[ncol]; check = true: relative errors per column into rel_mass / rel_energy and their MaxLoc

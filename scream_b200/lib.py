@@ -21,6 +21,7 @@ LIB_PATH = os.environ.get("P3B200_LIB", os.path.join(PKG_DIR, "libp3b200.so"))  
 LIB_PATHS = {"product": LIB_PATH, "parity": os.path.join(PKG_DIR, "libp3b200_parity.so")}
 TABLE_BLOB = os.path.join(PKG_DIR, "data", "p3_lookup_table_1.v4.1.1.f64")
 NUM_FIELDS = len(FIELDS)
+STATIC_BUDGET_MAX_COLS = 32768   # P3B200_STATIC_BUDGET_MAX_COLS (include/p3_b200.h)
 
 # every symbol include/p3_b200.h declares
 ABI_SYMBOLS = [
@@ -30,7 +31,7 @@ ABI_SYMBOLS = [
     "p3b200_error_summary", "p3b200_main_host", "p3b200_last_kernel_ms", "p3b200_last_phase_ms",
     "p3b200_last_sed_concurrent", "p3b200_last_phase_a_ms",
     "p3b200_main_preamble", "p3b200_column_conservation_begin", "p3b200_column_conservation_check", "p3b200_column_conservation_get",
-    "p3b200_water_energy_totals", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
+    "p3b200_water_energy_totals", "p3b200_water_energy_totals_static", "p3b200_set_default_tables", "p3b200_preamble", "p3b200_postamble",
     "p3b200_property_checks", "p3b200_postamble_checked", "p3b200_repair_qv", "p3b200_main_postamble",
     "p3b200_p3_main_f",
 ]
@@ -111,6 +112,8 @@ def lib(flavour="product"):
         L.p3b200_column_conservation_get.argtypes = [ctypes.c_void_p, ctypes.c_int32] + [ctypes.c_void_p] * 4
         L.p3b200_water_energy_totals.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields), ctypes.POINTER(P3B200Infra),
                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.p3b200_water_energy_totals_static.argtypes = [ctypes.c_void_p, ctypes.POINTER(P3B200Fields),
+                                                        ctypes.POINTER(P3B200Infra), ctypes.c_void_p, ctypes.c_void_p]
         L.p3b200_set_default_tables.argtypes = [ctypes.POINTER(P3B200Tables), ctypes.c_int]
         L.p3b200_tables_read_text.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
         L.p3b200_tables_read_blob.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(P3B200Tables)]
@@ -327,6 +330,18 @@ class P3Handle:
                                                ctypes.c_void_p(stream) if stream else None, None, out.ctypes.data),
               "p3b200_water_energy_totals")
         return out
+
+    def water_energy_totals_static(self, fields, dt, totals4_dev, stream=None):
+        """The same totals through the allocation-free entry point (p3b200_water_energy_totals_static): the scratch is
+        a fixed device array of the library, the 4 doubles land in `totals4_dev` (a device tensor of the caller's) in
+        stream order; nothing is copied back or synchronised.  At most STATIC_BUDGET_MAX_COLS columns."""
+        f, ncol, nlev = self.fields_struct(fields, host=False)
+        infra = self._infra(ncol, nlev, dt, True, True, True)
+        assert totals4_dev.is_cuda and totals4_dev.dtype.itemsize == 8 and totals4_dev.numel() >= 4
+        check(self._L.p3b200_water_energy_totals_static(self._h, ctypes.byref(f), ctypes.byref(infra),
+                                                      ctypes.c_void_p(stream) if stream else None,
+                                                      ctypes.c_void_p(totals4_dev.data_ptr())),
+              "p3b200_water_energy_totals_static")
 
     def preamble(self, fields, stream=None):
         """p3_preamble on device tensors (dict keyed by PREAMBLE_FIELDS, all (ncol, nlev) with one column stride)."""
