@@ -208,10 +208,13 @@ struct PhaseA {
       const float Tf = (float)T0;
 #if defined(__CUDA_ARCH__)
       const float e = __expf(9.550426f - __fdividef(5723.265f, Tf) + 3.53068f * __logf(Tf) - 0.00728332f * Tf);
+      // approximate division (2 ulp, inside the estimate's error budget): the IEEE one took its out-of-line slow path
+      // on every level with qv = 0
+      const float ratio = __fdividef((float)qv0 * fmaxf((float)pres, 1.e-3f), (float)C::ep_2 * e);
 #else
       const float e = std::exp(9.550426f - 5723.265f / Tf + 3.53068f * std::log(Tf) - 0.00728332f * Tf);
-#endif
       const float ratio = (float)qv0 * fmaxf((float)pres, 1.e-3f) / ((float)C::ep_2 * e);
+#endif
       const bool clear95 = fabsf(ratio - 0.95f) > 2.e-3f;
       const bool clear90 = !small_ice || fabsf(ratio - 0.90f) > 2.e-3f;
       if (clear95 && clear90 && ratio < 1.e30f) {     // NaN/inf estimates fall through to the exact path
@@ -733,7 +736,9 @@ struct Sediment {
           } else {
             Real qi_i, ni_i, qm_i, bm_i;
             if (first) P::incloud_ice(q[j], n[j], qm[j], bm[j], icf[j], 1 / cflw[j], qi_i, ni_i, qm_i, bm_i);
-            else { qi_i = q[j] / cf[j]; ni_i = n[j] / cf[j]; qm_i = qm[j] / cf[j]; bm_i = bm[j] / cf[j]; }   // exact: rho_rime = qm/bm is ill-conditioned
+            else {   // exact quotients: rho_rime = qm/bm is ill-conditioned.  div_z: most levels of a window are empty
+              qi_i = P::div_z(q[j], cf[j]); ni_i = P::div_z(n[j], cf[j]); qm_i = P::div_z(qm[j], cf[j]); bm_i = P::div_z(bm[j], cf[j]);
+            }
             if (qi_i > qsmall) {
               ni_i = P::rmax(ni_i, C::NSMALL);
               const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
@@ -808,6 +813,158 @@ struct Sediment {
       if (SP == SP_ICE)   a.f[F_PRECIP_ICE_SURF][col] += surf;                // p3_ice_sed_impl.hpp:192 (only ice writes it)
       int* d = a.diag + col * D_NUM;
       d[dbase + 1] = k_qxbot; d[dbase + 2] = nsub;
+      if (err) WP::atomic_or(d + D_ERROR, err);
+    }
+  }
+
+  // ---- ice on tall windows: the same sub-step loop with the window in a per-warp array instead of registers ----
+  // run() unrolls the JW slots of a lane: for ice at JW = 4 that is an 83 KB loop body, and with every warp of an SM at
+  // a different place in it the kernel waits on instruction fetch (stall "no instruction" 5 warps per issue, issue
+  // slots 36 % busy; profiles/r02h_sediment_random_ic_ncu_summary.txt).  Here the slots are visited by a ROLLED loop:
+  // one copy of the fall-speed block and one of the upwind block, the state of slot j read from and written back to
+  // `st` (shared memory on the device: RS_NUM arrays of JW*WS values, element j*WS + lane: conflict-free).  Level by
+  // level the arithmetic is the one of run(): same expressions, same order; the four upwind sweeps of a sub-step are
+  // independent of each other and become one sweep over the slots that carries four inflow values.
+  enum RolledState { RS_Q, RS_N, RS_QM, RS_BM, RS_RHO, RS_IRHO, RS_IDZ, RS_CF, RS_FAC, RS_VQ, RS_VN, RS_NUM };
+  static constexpr int rolled_state_size = RS_NUM * JW * WS;
+
+  static P3_HD void run_rolled(const WP& w, const MainArgs<Real>& a, int64_t col, int k_qxtop, int k_qxbot, Real* st) {
+    static_assert(SP == SP_ICE, "the rolled window is built for ice_sedimentation");
+    constexpr int NS = JW * WS;
+    const int lane = w.lane();
+    const int nk = a.nk, kbot = nk - 1;
+    const Real qsmall = C::QSMALL;
+    Real* const g_q = col_ptr(a, F_QI, col); Real* const g_n = col_ptr(a, F_NI, col);
+    Real* const g_qm = col_ptr(a, F_QM, col); Real* const g_bm = col_ptr(a, F_BM, col);
+    const Real* const g_cf = col_ptr(a, F_CLD_FRAC_I, col);
+    const Real* const g_cfl = col_ptr(a, F_CLD_FRAC_L, col);
+    const Real* const g_dz = col_ptr(a, F_DZ, col); const Real* const g_dpres = col_ptr(a, F_DPRES, col);
+    const Real inv_dt = 1 / a.dt;
+    const int kw = k_qxtop;
+    const int nslot = (nk - kw + WS - 1) / WS;          // slots that hold a level (<= JW by the launch's window class)
+    Real* const s_q = st + RS_Q * NS + lane;   Real* const s_n = st + RS_N * NS + lane;
+    Real* const s_qm = st + RS_QM * NS + lane; Real* const s_bm = st + RS_BM * NS + lane;
+    Real* const s_rho = st + RS_RHO * NS + lane; Real* const s_irho = st + RS_IRHO * NS + lane;
+    Real* const s_idz = st + RS_IDZ * NS + lane; Real* const s_cf = st + RS_CF * NS + lane;
+    Real* const s_fac = st + RS_FAC * NS + lane; Real* const s_vq = st + RS_VQ * NS + lane;
+    Real* const s_vn = st + RS_VN * NS + lane;
+#pragma unroll 1
+    for (int j = 0; j < nslot; ++j) {
+      const int k = kw + lane + j * WS, o = j * WS;
+      const bool in = k < nk;
+      const Real q = in ? g_q[k] : Real(0), n = in ? g_n[k] : Real(0);
+      const Real qm = in ? g_qm[k] : Real(0), bm = in ? g_bm[k] : Real(0);
+      const Real dz = in ? P3_LDG(g_dz + k) : Real(1), dp = in ? P3_LDG(g_dpres + k) : Real(1);
+      const Real cf = in ? P3_LDG(g_cf + k) : Real(1);
+      s_q[o] = q; s_n[o] = n; s_qm[o] = qm; s_bm[o] = bm; s_cf[o] = cf;
+      if (in) {
+        const Real rho = dp / dz / C::gravit;             // p3_main_impl_part1.hpp:93
+        s_rho[o] = rho; s_irho[o] = 1 / rho; s_idz[o] = 1 / dz;   // p3_main_impl.hpp:57
+        s_fac[o] = -1;    // rhofaci (p3_main_impl_part1.hpp:106) is evaluated when the level first holds ice
+      } else {
+        s_rho[o] = 1; s_irho[o] = 1; s_idz[o] = 0; s_fac[o] = 0;
+      }
+    }
+    // a lane only ever touches its own elements of `st`: no synchronisation inside the loop
+
+    int nsub = 0, err = 0;
+    Real dt_left = a.dt, prt_local = 0;
+    bool first = true;
+    while (dt_left > C::dt_left_tol) {
+      const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
+      Real Co_loc = 0;
+#pragma unroll 1
+      for (int j = 0; j < nslot && kw + j * WS <= k_qxbot; ++j) {     // warp-uniform: slots the front has reached
+        const int k = kw + lane + j * WS, o = j * WS;
+        Real vq = 0, vn = 0;
+        Real fac = s_fac[o];
+        const Real q = s_q[o], inv_rho = s_irho[o];
+        // rhofaci for the whole slot the first time any of its levels holds ice; all lanes take part in the vote
+        if (w.any(fac < 0 && k <= k_qxbot && q > 0)) {
+          if (fac < 0) { fac = P::x_pow(C::RHO_600MB * inv_rho, sp(.54)); s_fac[o] = fac; }
+        }
+        if (k <= k_qxbot) {
+          const Real cf = s_cf[o];
+          const Real n = s_n[o], qm = s_qm[o], bm = s_bm[o];
+          Real qi_i, ni_i, qm_i, bm_i;
+          if (first) P::incloud_ice(q, n, qm, bm, 1 / cf, 1 / P3_LDG(g_cfl + k), qi_i, ni_i, qm_i, bm_i);
+          else {   // exact quotients: rho_rime = qm/bm is ill-conditioned.  div_z: most levels of a window are empty
+            qi_i = P::div_z(q, cf); ni_i = P::div_z(n, cf); qm_i = P::div_z(qm, cf); bm_i = P::div_z(bm, cf);
+          }
+          if (qi_i > qsmall) {
+            ni_i = P::rmax(ni_i, C::NSMALL);
+            const Real rhop = P::calc_bulk_rho_rime(qi_i, qm_i, bm_i, a.ro);
+            s_qm[o] = qm_i * cf;
+            s_bm[o] = bm_i * cf;
+            typename P::IceLoc ti;
+            P::template lookup_ice<true>(qi_i, ni_i, qm_i, rhop, ti);
+            Real tv_ni_fallspd, tv_qi_fallspd, tv_ni_lammax, tv_ni_lammin;
+            P::apply_table_ice2(0, a.tb.ice, ti, tv_ni_fallspd, tv_qi_fallspd);
+            P::apply_table_ice2(6, a.tb.ice, ti, tv_ni_lammax, tv_ni_lammin);
+            ni_i = P::rmin(ni_i, tv_ni_lammax * ni_i);
+            ni_i = P::rmax(ni_i, tv_ni_lammin * ni_i);
+            s_n[o] = ni_i * cf;
+            vq = a.ro.ice_sedimentation_factor * tv_qi_fallspd * fac;
+            vn = a.ro.ice_sedimentation_factor * tv_ni_fallspd * fac;
+          }
+          const Real Co = vq * dt_left * s_idz[o];
+          if (Co > Co_loc) Co_loc = Co;
+        }
+        s_vq[o] = vq; s_vn[o] = vn;
+      }
+      const Real Co_max = w.max_nonneg(Co_loc);
+      // generalized_sedimentation: p3_upwind_impl.hpp:97-129
+      if (!(Co_max >= 0)) err |= 4;
+      const int tmpint1 = static_cast<int>(Co_max + 1);
+      const Real dt_sub = dt_left / tmpint1;
+      Real pl_bm = 0, pl_qm = 0, pl_n = 0, pl_q = 0;      // lane 0: flux out of the last lane of the previous slot
+#pragma unroll 1
+      for (int j = 0; j < nslot && kw + j * WS <= k_temp; ++j) {
+        const int k = kw + lane + j * WS, o = j * WS;
+        const bool in = k <= k_temp;
+        const bool has_v = kw + j * WS <= k_qxbot;         // a slot the front enters in this sub-step has no fall speed yet
+        const Real Vq = has_v ? s_vq[o] : Real(0), Vn = has_v ? s_vn[o] : Real(0);
+        const Real rho = s_rho[o], inv_rho = s_irho[o], inv_dz = s_idz[o];
+        Real r[4] = {s_bm[o], s_qm[o], s_n[o], s_q[o]};
+        const Real V[4] = {Vq, Vq, Vn, Vq};
+        Real pl[4] = {pl_bm, pl_qm, pl_n, pl_q};
+        Real fq = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const Real f = in ? V[i] * r[i] * rho : Real(0);
+          // one rotation serves both: lanes > 0 receive the flux of the level above, lane 0 the flux out of this
+          // slot's last lane, which is what lane 0 (and only lane 0) needs in the next slot
+          const Real rot = w.rot_up1(f);
+          const Real up = (lane == 0) ? pl[i] : rot;
+          pl[i] = rot;
+          const Real fluxdiv = (up - f) * inv_dz;
+          const Real r_new = r[i] + fluxdiv * dt_sub * inv_rho;
+          r[i] = in ? r_new : r[i];
+          if (i == 3) fq = f;
+        }
+        pl_bm = pl[0]; pl_qm = pl[1]; pl_n = pl[2]; pl_q = pl[3];
+        s_bm[o] = r[0]; s_qm[o] = r[1]; s_n[o] = r[2]; s_q[o] = r[3];
+        const Real prt_new = prt_local + fq * dt_sub;
+        prt_local = (k == kbot && k_qxbot == kbot) ? prt_new : prt_local;
+      }
+      if (k_qxbot != kbot) k_qxbot += 1;
+      dt_left -= dt_sub;
+      first = false;
+      ++nsub;
+    }
+    // write back the part of the window the front reached
+#pragma unroll 1
+    for (int j = 0; j < nslot && kw + j * WS <= k_qxbot; ++j) {
+      const int k = kw + lane + j * WS, o = j * WS;
+      if (k <= k_qxbot) { g_q[k] = s_q[o]; g_n[k] = s_n[o]; g_qm[k] = s_qm[o]; g_bm[k] = s_bm[o]; }
+    }
+    const Real prt_accum = w.shfl_from(prt_local, (kbot - kw) % WS);   // only the lane owning kbot accumulated
+    const Real surf = prt_accum * C::INV_RHO_H2O * inv_dt;
+    err = w.or_int(err);
+    if (lane == 0) {
+      a.f[F_PRECIP_ICE_SURF][col] += surf;                // p3_ice_sed_impl.hpp:192 (only ice writes it)
+      int* d = a.diag + col * D_NUM;
+      d[D_QI_KTOP + 1] = k_qxbot; d[D_QI_KTOP + 2] = nsub;
       if (err) WP::atomic_or(d + D_ERROR, err);
     }
   }

@@ -54,6 +54,8 @@ struct WarpDev {
   // value of the previous lane (lane 0 keeps its own: callers patch it) / of lane `src`
   template <class R> __device__ __forceinline__ R shfl_up1(R v) const { return __shfl_up_sync(FULL, v, 1); }
   template <class R> __device__ __forceinline__ R shfl_from(R v, int src) const { return __shfl_sync(FULL, v, src); }
+  // rotate by one lane: lane l receives lane l-1's value, lane 0 receives the last lane's
+  template <class R> __device__ __forceinline__ R rot_up1(R v) const { return __shfl_sync(FULL, v, (lane() + 31) & 31); }
 };
 
 #if !defined(P3B200_A_THREADS)
@@ -269,6 +271,10 @@ p3_column_finish(const __grid_constant__ MainArgs<Real> a) {
 constexpr int sed_min_blocks(int SP, int JW) {
   return JW == 1 ? (SP == SP_RAIN ? P3B200_B_RAIN1 : 8) : JW == 2 ? 5 : JW == 4 ? (SP == SP_ICE ? P3B200_B_ICE4 : 3) : 2;
 }
+#if !defined(P3B200_ICE_ROLLED)
+#define P3B200_ICE_ROLLED 1
+#endif
+__host__ __device__ constexpr bool sed_rolled(int SP, int JW) { return P3B200_ICE_ROLLED && SP == SP_ICE && JW == 4; }
 __host__ __device__ constexpr int sed_class(int need) { return need <= 1 ? 1 : need <= 2 ? 2 : need <= 4 ? 4 : 8; }
 
 template <typename Real, int SP, int JW>
@@ -307,7 +313,14 @@ p3_sediment(const __grid_constant__ MainArgs<Real> a, unsigned int* __restrict__
       todo &= todo - 1;
       const int kt = __shfl_sync(WarpDev::FULL, ktop, src);
       const int kb = __shfl_sync(WarpDev::FULL, kbot, src);
-      Sediment<Real, WarpDev, SP, JW>::run(w, a, c0 + src, kt, kb, rain_tab);
+      if constexpr (sed_rolled(SP, JW)) {
+        // ice on tall windows: the window lives in shared memory and the slots are a rolled loop (Sediment::run_rolled)
+        using S = Sediment<Real, WarpDev, SP, JW>;
+        __shared__ Real s_state[B_WARPS][S::rolled_state_size];
+        S::run_rolled(w, a, c0 + src, kt, kb, s_state[threadIdx.x >> 5]);
+      } else {
+        Sediment<Real, WarpDev, SP, JW>::run(w, a, c0 + src, kt, kb, rain_tab);
+      }
     }
   }
 }

@@ -6,6 +6,8 @@
 #include "../../scream_b200/csrc/p3_column.cuh"
 #include "../../scream_b200/csrc/p3_host.hpp"
 
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 namespace {
@@ -22,6 +24,7 @@ struct WarpSim {
   static void atomic_or(int* p, int v) { *p |= v; }
   template <class R> R shfl_up1(R v) const { return v; }
   template <class R> R shfl_from(R v, int) const { return v; }
+  template <class R> R rot_up1(R v) const { return v; }
 };
 
 template <typename Real>
@@ -56,6 +59,9 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   if (!diag) { own_diag.assign(size_t(ncol) * D_NUM, 0); diag = own_diag.data(); }
   a.diag = diag; a.queue = nullptr;
   WarpSim w;
+  const char* ice_env = std::getenv("P3B200_HOSTSIM_ICE");
+  const bool ice_rolled = !(ice_env && std::strcmp(ice_env, "unrolled") == 0);
+  std::vector<Real> ice_state;
   // the three phases in the order the kernels run them (p3_kernel.cu: launch_main)
   for (int i = 0; i < ncol; ++i) PhaseA<Real>::run_column_host(a, i);
   for (int i = 0; i < ncol; ++i) {
@@ -68,7 +74,12 @@ int run(const P3B200Tables* t, void* const* fields, const int64_t* strides, int 
   }
   for (int i = 0; i < ncol; ++i) {
     const int* d = diag + size_t(i) * D_NUM;
-    if (d[D_QI_KTOP] >= 0) Sediment<Real, WarpSim, SP_ICE, p3b200::MAX_NLEV>::run(w, a, i, d[D_QI_KTOP], d[D_QI_KBOT]);
+    if (d[D_QI_KTOP] < 0) continue;
+    // the device runs tall ice windows through Sediment::run_rolled (window in shared memory, slots as a rolled loop)
+    // and short ones through run(): both here, selected by P3B200_HOSTSIM_ICE=rolled|unrolled (default rolled)
+    using SI = Sediment<Real, WarpSim, SP_ICE, p3b200::MAX_NLEV>;
+    if (ice_rolled) { ice_state.resize(SI::rolled_state_size); SI::run_rolled(w, a, i, d[D_QI_KTOP], d[D_QI_KBOT], ice_state.data()); }
+    else SI::run(w, a, i, d[D_QI_KTOP], d[D_QI_KBOT]);
   }
   for (int i = 0; i < ncol; ++i) {
     const bool full = diag[size_t(i) * D_NUM + D_HYDRO_PART2] == 1;

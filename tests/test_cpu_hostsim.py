@@ -110,3 +110,25 @@ def test_parity_flavour_is_bit_identical_to_the_shared_math_oracle(nlev, dt, dty
     for n in OUTPUTS:
         assert np.array_equal(ref[n], got[n], equal_nan=True), n
     assert np.array_equal(d_ref[:, :12], d_got[:, :12])
+
+
+@pytest.mark.parametrize("flavour", ["exact", "product", "parity"])
+@pytest.mark.parametrize("nlev,dt", [(72, 1800.0), (128, 300.0)])
+def test_rolled_ice_window_is_bit_identical_to_the_unrolled_one(monkeypatch, flavour, nlev, dt):
+    """Sediment::run_rolled (ice on tall windows: state in an array, slots as a rolled loop — what
+    p3_sediment<ice, 4> runs on the device) against Sediment::run (slots unrolled in registers): every output and the
+    sub-step counts bit for bit, on columns with ice windows of all heights.  Here a slot is one level (warp of size
+    1), so every level boundary exercises the carry between slots and the slot the front enters."""
+    from scream_b200.fields import OUTPUTS
+    f = ic_cases.make_random(512, nlev)
+    parity.zero_outputs(f)
+    a, b = parity.clone(f), parity.clone(f)
+    monkeypatch.setenv("P3B200_HOSTSIM_ICE", "unrolled")
+    d_a = hostsim_lib.p3_main(a, dt, True, True, flavour=flavour)
+    monkeypatch.setenv("P3B200_HOSTSIM_ICE", "rolled")
+    d_b = hostsim_lib.p3_main(b, dt, True, True, flavour=flavour)
+    assert (d_a[:, 9] >= 0).sum() > 100          # D_QI_KTOP: most columns sediment ice
+    assert d_a[:, 11].max() > 1                   # D_QI_NSUB: several sub-steps somewhere
+    for n in OUTPUTS:
+        assert np.array_equal(a[n], b[n], equal_nan=True), n
+    assert np.array_equal(d_a, d_b)

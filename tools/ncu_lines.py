@@ -50,7 +50,11 @@ def disasm(cubin, kernel):
 def main():
     rep, cubin, kernel = sys.argv[1:4]
     top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 40
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    if rep.endswith(".csv") or rep.endswith(".csv.gz"):   # `ncu -i <rep> --page source --csv`, exported on the GPU box (tools/ncu_export.sh)
+        import gzip
+        raw = (gzip.open(rep, "rt") if rep.endswith(".gz") else open(rep)).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     lines = raw.splitlines()
     # one section per profiled launch: "Kernel Name",<demangled> then the "Address",... table
     want = sys.argv[sys.argv.index("--launch") + 1] if "--launch" in sys.argv else None
@@ -94,6 +98,20 @@ def main():
             if v:
                 stall_by_phase[phase][c] += v
     print(f"total warp instructions {tot_i:,}  samples {tot_s:,}")
+    if "--calls" in sys.argv:
+        # every CALL that was executed: a call site of an out-of-line routine (fp64 division / reciprocal slow paths,
+        # pow) counts the warps that left the inline fast path there
+        print("\n== executed CALL sites ==")
+        sites = []
+        for r in rows:
+            off = int(r["Address"], 16) - base
+            frames, text, sub = dis.get(off, ([], "", None))
+            n = int(r["Instructions Executed"] or 0)
+            if "CALL" in text and n:
+                sites.append((n, off, text, frames))
+        for n, off, text, frames in sorted(sites, reverse=True)[:top]:
+            fr = " <- ".join(f"{f}:{l}" for f, l in frames[:4])
+            print(f"  {n:12,d}  {text[:60]:60s} {fr}")
     print("\n== by device subroutine (called, not inlined) ==")
     for k, v in by_sub.most_common(12):
         print(f"  {str(k):40s} {100*v/tot_i:6.2f}% inst")

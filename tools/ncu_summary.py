@@ -22,7 +22,10 @@ WANT = ["Kernel Name", "launch__grid_size", "launch__block_size", "launch__regis
 
 
 def main():
-    raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if sys.argv[1].endswith(".csv"):      # `ncu -i <rep> --page raw --csv`, exported on the GPU box (tools/ncu_export.sh)
+        raw = open(sys.argv[1]).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     head, units = rows[0], rows[1]
     stalls = [h for h in head if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
