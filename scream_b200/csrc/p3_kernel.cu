@@ -207,7 +207,7 @@ __host__ __device__ constexpr int part2_min_blocks(int grp) {
 }
 
 template <typename Real, int GRP, bool UNI>
-__global__ void __launch_bounds__(P2_THREADS, part2_min_blocks(GRP))
+__global__ void __launch_bounds__(P2_THREADS, part2_min_blocks(GRP) * (128 / P2_THREADS))   // the budgets are per 128 threads
 p3_part2(const __grid_constant__ MainArgs<Real> a, const int ntiles, const int tile_cols, const unsigned div_magic) {
   const int lane = threadIdx.x & 31;
   const int nk = a.nk;
@@ -260,13 +260,13 @@ p3_column_finish(const __grid_constant__ MainArgs<Real> a) {
 // `chunk` (<= 32) consecutive columns from the launch's own atomic counter; lane i of the warp looks up
 // the range of column i of the chunk, a ballot selects the columns of this launch's class.
 // resident CTAs per SM each sedimentation instantiation is compiled for (its register budget), measured per
-// species: rain (JW=1) is issue-bound and likes 80 registers, ice on tall windows is latency-bound and is faster
-// with 16 warps/SM and a few spills than with 12 and none
+// species: rain (JW=1) is issue-bound and likes 80 registers; ice on tall windows (rolled loop over a shared-memory
+// window, Sediment::run_rolled) is bound by dependent-issue latency and takes as many warps as its shared memory allows
 #if !defined(P3B200_B_RAIN1)
 #define P3B200_B_RAIN1 6
 #endif
 #if !defined(P3B200_B_ICE4)
-#define P3B200_B_ICE4 4
+#define P3B200_B_ICE4 5   // the rolled shared-memory window needs 94 registers: 5 CTAs (20 warps, 5 x 45 KB) per SM; 4: +3 ms on the random IC
 #endif
 constexpr int sed_min_blocks(int SP, int JW) {
   return JW == 1 ? (SP == SP_RAIN ? P3B200_B_RAIN1 : 8) : JW == 2 ? 5 : JW == 4 ? (SP == SP_ICE ? P3B200_B_ICE4 : 3) : 2;
