@@ -218,10 +218,13 @@ p3_part2(const __grid_constant__ MainArgs<Real> a, const int ntiles, const int t
   if (e0 >= e1) return;
   const unsigned short* wl = a.wl_idx + (int64_t)t * A_TILE_LEVELS;
   const int64_t col0 = (int64_t)t * tile_cols;
+  // the work-list entry of a sub-group is read one iteration ahead: its latency is not in front of the level's loads
+  int idx_next = (e0 + lane < e1) ? (int)wl[e0 + lane] : 0;
   for (int base = e0; base < e1; base += 32) {
     const int e = base + lane;
+    const int idx = idx_next;
+    idx_next = (e + 32 < e1) ? (int)wl[e + 32] : 0;
     if (e < e1) {
-      const int idx = wl[e];
       const int c = (int)(((unsigned)idx * div_magic) >> 24);
       const int k = idx - c * nk;
       const int64_t col = col0 + c;
@@ -263,7 +266,7 @@ p3_column_finish(const __grid_constant__ MainArgs<Real> a) {
 // species: rain (JW=1) is issue-bound and likes 80 registers; ice on tall windows (rolled loop over a shared-memory
 // window, Sediment::run_rolled) is bound by dependent-issue latency and takes as many warps as its shared memory allows
 #if !defined(P3B200_B_RAIN1)
-#define P3B200_B_RAIN1 6
+#define P3B200_B_RAIN1 7   // 72 registers, no spills: 14.8 -> 14.5 ms on the mixed IC; 8 (64 registers): 15.0 ms
 #endif
 #if !defined(P3B200_B_ICE4)
 #define P3B200_B_ICE4 5   // the rolled shared-memory window needs 94 registers: 5 CTAs (20 warps, 5 x 45 KB) per SM; 4: +3 ms on the random IC
