@@ -173,9 +173,10 @@ struct PhaseA {
     const Real c1 = -Real(1) + Real(1) / C::ep_2;
     const Real T_virtual = pr.T * (Real(1) + c1 * in.qv);
     cp.template p<F_DZ>(a)[k] = (C::RD / C::gravit) * pr.pd * T_virtual / pr.pmid;
-    in.qv = in.qv * pr.pd / pr.pdd; in.qc = in.qc * pr.pd / pr.pdd;
-    in.qr = in.qr * pr.pd / pr.pdd; in.qi = in.qi * pr.pd / pr.pdd;
-    cp.template p<F_QV_PREV>(a)[k] = pr.qv_prev * pr.pd / pr.pdd;
+    // div_z: a clear level's mixing ratios are exactly 0, and a zero numerator sends the fp64 division out of line
+    in.qv = P::div_z(in.qv * pr.pd, pr.pdd); in.qc = P::div_z(in.qc * pr.pd, pr.pdd);
+    in.qr = P::div_z(in.qr * pr.pd, pr.pdd); in.qi = P::div_z(in.qi * pr.pd, pr.pdd);
+    cp.template p<F_QV_PREV>(a)[k] = P::div_z(pr.qv_prev * pr.pd, pr.pdd);
     const Real ex = P::x_pow(pr.pmid / C::P0, C::RD * C::INV_CP);
     in.inv_exner = Real(1.0) / ex;
     in.th = pr.T / ex;
@@ -195,7 +196,7 @@ struct PhaseA {
 #pragma unroll
     for (int i = 0; i < 5; ++i) v[i] = *p[i];
 #pragma unroll
-    for (int i = 0; i < 5; ++i) *p[i] = v[i] * pr.pd / pr.pdd;
+    for (int i = 0; i < 5; ++i) *p[i] = P::div_z(v[i] * pr.pd, pr.pdd);
   }
 
   // Single-precision estimate of qv / qv_sat_i(T0, pres) on a cold level (relative error < 1e-4: fp32

@@ -42,8 +42,9 @@ struct PrePost {
   // exner_function :88-97
   static __device__ __forceinline__ Real exner(Real p) { return Phys<Real>::x_pow(p / C::P0, C::RD * C::INV_CP); }
   // calculate_drymmr_from_wetmmr_dp_based :375-379 / calculate_wetmmr_from_drymmr_dp_based :327-331
-  static __device__ __forceinline__ Real dry(Real wet, Real pd, Real pdd) { return wet * pd / pdd; }
-  static __device__ __forceinline__ Real wet(Real dry, Real pd, Real pdd) { return dry * pdd / pd; }
+  // div_z: most mixing ratios of most levels are exactly 0, and a zero numerator sends the fp64 division out of line
+  static __device__ __forceinline__ Real dry(Real wet, Real pd, Real pdd) { return Phys<Real>::div_z(wet * pd, pdd); }
+  static __device__ __forceinline__ Real wet(Real dry, Real pd, Real pdd) { return Phys<Real>::div_z(dry * pdd, pd); }
 };
 
 
