@@ -849,8 +849,12 @@ struct Sediment {
     Real* const s_idz = st + RS_IDZ * NS + lane; Real* const s_cf = st + RS_CF * NS + lane;
     Real* const s_fac = st + RS_FAC * NS + lane; Real* const s_vq = st + RS_VQ * NS + lane;
     Real* const s_vn = st + RS_VN * NS + lane;
-#pragma unroll 1
-    for (int j = 0; j < nslot; ++j) {
+    // A slot is loaded (7 loads, 3 divisions per level) when the front first reaches it, not before: a window spans
+    // everything down to the surface, but the front advances one level per sub-step — a column with ice aloft and a
+    // single sub-step used to set up three slots to use one.  A lane only ever touches its own elements of `st`: no
+    // synchronisation anywhere.
+    int nready = 0;
+    auto load_slot = [&](int j) {
       const int k = kw + lane + j * WS, o = j * WS;
       const bool in = k < nk;
       const Real q = in ? g_q[k] : Real(0), n = in ? g_n[k] : Real(0);
@@ -865,14 +869,15 @@ struct Sediment {
       } else {
         s_rho[o] = 1; s_irho[o] = 1; s_idz[o] = 0; s_fac[o] = 0;
       }
-    }
-    // a lane only ever touches its own elements of `st`: no synchronisation inside the loop
+    };
 
     int nsub = 0, err = 0;
     Real dt_left = a.dt, prt_local = 0;
     bool first = true;
     while (dt_left > C::dt_left_tol) {
       const int k_temp = (k_qxbot == kbot) ? k_qxbot : k_qxbot + 1;
+#pragma unroll 1
+      while (nready < nslot && kw + nready * WS <= k_temp) { load_slot(nready); ++nready; }   // warp-uniform
       Real Co_loc = 0;
 #pragma unroll 1
       for (int j = 0; j < nslot && kw + j * WS <= k_qxbot; ++j) {     // warp-uniform: slots the front has reached
