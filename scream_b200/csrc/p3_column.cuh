@@ -766,7 +766,7 @@ struct Sediment {
       // generalized_sedimentation: p3_upwind_impl.hpp:97-129
       if (!(Co_max >= 0)) err |= 4;
       const int tmpint1 = static_cast<int>(Co_max + 1);
-      const Real dt_sub = dt_left / tmpint1;
+      const Real dt_sub = P::div_by_count(dt_left, tmpint1);
       Real flux[JW], ftmp[JW];
       if (SP == SP_ICE) {
         upwind(w, lane, kw, k_temp, dt_sub, Vq, bm, rho, inv_rho, inv_dz, ftmp);
@@ -922,7 +922,7 @@ struct Sediment {
       // generalized_sedimentation: p3_upwind_impl.hpp:97-129
       if (!(Co_max >= 0)) err |= 4;
       const int tmpint1 = static_cast<int>(Co_max + 1);
-      const Real dt_sub = dt_left / tmpint1;
+      const Real dt_sub = P::div_by_count(dt_left, tmpint1);
       Real pl_bm = 0, pl_qm = 0, pl_n = 0, pl_q = 0;      // lane 0: flux out of the last lane of the previous slot
 #pragma unroll 1
       for (int j = 0; j < nslot && kw + j * WS <= k_temp; ++j) {
