@@ -78,7 +78,7 @@ struct MainArgs {
   // p3_main fields themselves (mixing ratios in place, inv_exner, th, the three cloud fractions, dz, qv_prev).
   const Real *pre_pmid, *pre_pd, *pre_pdd, *pre_T, *pre_cft;
   // phase A scratch owned by the handle (p3_abi.cpp), valid between the classification pass and the column finish:
-  unsigned short* wl_idx;  // [ntiles][A_TILE_LEVELS] per tile: tile-local level indices (col_in_tile*nk + k) of the levels part2 has to run on, sorted by class key
+  unsigned short* wl_idx;  // [ntiles][A_TILE_LEVELS] per tile: tile-local level indices (col_in_tile*nk + k) of the levels part2 has to run on, ordered by process group, index order inside a group
   int*            wl_off;  // [ntiles][8]: start of each process group's segment in the tile's list; [6] = number of entries
   unsigned char*  lvlflags;// [ncol*nk] per level after part2: LF_* bits (species present, hydrometeors, error bits); 0 on skip_all levels
 };
@@ -110,14 +110,14 @@ struct ColAddr {
 //          skip_all gate (p3_main_impl_part2.hpp:121-127).  A skip_all level is COMPLETE after part1 —
 //          its post-part1 state is stored here from 7 loads.  Any other level is only classified: the
 //          pass returns a sort key (which species are present, temperature regime) and stores nothing.
-//   pass 2 (the classified levels, sorted by key so that the 32 lanes of a warp run the same process
-//          branches): init + part1 + part2 from the level's untouched inputs, stores, and the
+//   pass 2 (the classified levels, ordered by process group = temperature regime x ice present, in index order
+//          inside a group): init + part1 + part2 from the level's untouched inputs, stores, and the
 //          per-column reductions (hydrometeorsPresent after part2, find_top/find_bottom of the three
 //          sedimenting species) into a small per-column accumulator.
 //
 // The two passes are separate kernels (p3_kernel.cu): the classification pass is a streaming kernel at the
 // register budget of a streaming kernel; part2 runs as one launch per PROCESS GROUP (temperature regime x ice
-// present, Phys::part2_level<GRP>) on the class-sorted work lists the classification pass leaves in global memory,
+// present, Phys::part2_level<GRP>) on the group-ordered work lists the classification pass leaves in global memory,
 // each group compiled to the code and registers its regime needs.  What a level reports back to its column
 // (species present after part2 for find_top/find_bottom, hydrometeorsPresent, error bits) is one byte per level
 // (LF_*); a third, tiny kernel folds the bytes of a column into the integer diagnostics.
