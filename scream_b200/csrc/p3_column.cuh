@@ -332,6 +332,12 @@ struct PhaseA {
     typename P::Level L;
     L.qc = *g_qc; L.nc = *g_nc; L.qr = *g_qr; L.nr = *g_nr; L.qi = *g_qi;
     L.qm = *g_qm; L.ni = *g_ni; L.bm = *g_bm; L.qv = *g_qv; L.th = *g_th;
+    // which of the eight hydrometeor values are +0 in memory: an absent species stays absent on most levels, and a store
+    // of the +0 that is already there only dirties a sector the part2 launches then write back (they are bound by
+    // exactly that traffic)
+    const unsigned zero_in = (is_pos_zero(L.qc) ? 1u : 0u) | (is_pos_zero(L.nc) ? 2u : 0u) | (is_pos_zero(L.qr) ? 4u : 0u) |
+                             (is_pos_zero(L.nr) ? 8u : 0u) | (is_pos_zero(L.qi) ? 16u : 0u) | (is_pos_zero(L.qm) ? 32u : 0u) |
+                             (is_pos_zero(L.ni) ? 64u : 0u) | (is_pos_zero(L.bm) ? 128u : 0u);
     L.pres = P3_LDG(cp.template p<F_PRES>(a) + k); L.inv_exner = P3_LDG(cp.template p<F_INV_EXNER>(a) + k);
     L.cf_i = P3_LDG(cp.template p<F_CLD_FRAC_I>(a) + k); L.cf_l = P3_LDG(cp.template p<F_CLD_FRAC_L>(a) + k);
     L.cf_r = P3_LDG(cp.template p<F_CLD_FRAC_R>(a) + k);
@@ -388,8 +394,10 @@ struct PhaseA {
     // what find_top / find_bottom (p3_find_impl.hpp) and hydrometeorsPresent need from this level
     const int lf = (L.qc >= qsmall ? LF_QC : 0) | (L.qr >= qsmall ? LF_QR : 0) | (L.qi >= qsmall ? LF_QI : 0) |
                    (h ? LF_HYD : 0) | (err << LF_ERR_SHIFT);
-    *g_qc = L.qc; *g_nc = L.nc; *g_qr = L.qr; *g_nr = L.nr; *g_qi = L.qi;
-    *g_qm = L.qm; *g_ni = L.ni; *g_bm = L.bm; *g_qv = L.qv; *g_th = L.th;
+    auto put = [&](Real* p, Real v, unsigned bit) { if (!((zero_in & bit) && is_pos_zero(v))) *p = v; };
+    put(g_qc, L.qc, 1u); put(g_nc, L.nc, 2u); put(g_qr, L.qr, 4u); put(g_nr, L.nr, 8u); put(g_qi, L.qi, 16u);
+    put(g_qm, L.qm, 32u); put(g_ni, L.ni, 64u); put(g_bm, L.bm, 128u);
+    *g_qv = L.qv; *g_th = L.th;
     // the classification pass wrote zero tendencies, zero fluxes and the parked +-T_atm(init) for this level:
     // only a tendency whose bit pattern is not +0 needs a store
     if (!is_pos_zero(o.qv2qi_depos_tend))  cp.template p<F_QV2QI_DEPOS_TEND>(a)[k] = o.qv2qi_depos_tend;
