@@ -537,6 +537,8 @@ struct Sediment {
   }
 
   // rain_tab (rain only): the 300 x (vm, vn) slice of Tables::vmn for this run's mu_r column, or nullptr
+  // RFAST (rain only): the caller guarantees rain_tab != nullptr, and the generic table path is compiled out of the loop
+  template <bool RFAST = false>
   static P3_HD void run(const WP& w, const MainArgs<Real>& a, int64_t col, int k_qxtop, int k_qxbot,
                         const Real* rain_tab = nullptr) {
     const int lane = w.lane();
@@ -616,7 +618,7 @@ struct Sediment {
     const bool rain_fast = false;       // exact-order build: get_rain_dsd2 + lookup + apply_table as the reference calls them
     (void)rain_tab;
 #else
-    const bool rain_fast = (SP == SP_RAIN) && rain_tab != nullptr;
+    const bool rain_fast = (SP == SP_RAIN) && (RFAST || rain_tab != nullptr);
 #endif
 
     // rain, fast-table path: the in-cloud values of the NEXT sub-step are carried in registers (what
